@@ -1,0 +1,139 @@
+/*
+ * rtb.h -- C ABI of librtb.so, the B200 (sm_100a) ray-stepping engine that replaces the
+ * hot path of neyuru/RayTracing's RT_bench.py.
+ *
+ * The reference has no FFI layer: its boundary for this path is the Python call
+ *     trazar(selected_func, z, grd, show, step, divisor, user_choice)
+ *         -> (s_ray, d_ray, compute_times, errors)                  RT_bench.py:766-948
+ *     search_delta(option, z, grd, step, divisor, user_choice)      RT_bench.py:950-958
+ *     n_gradient(vector, grd, z) -> (n, [dn/dx, dn/dy])             RT_bench.py:141-156
+ * plus the module globals those functions read (gamma RT:725, N RT:797, GOLD_* RT:64-66).
+ * Each entry point below states which of these it replaces.  The Python shim that keeps
+ * the reference signatures lives in raytracing_b200/engine.py and binds this header with
+ * ctypes (raytracing_b200/_cabi.py); INTEGRATION.md shows the stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions: every function returns 0 on success and a negative rtb_status otherwise
+ * (never exits the process, cf. sys.exit() RT:1406); rtb_last_error() gives the text.
+ * One context per GPU, one CUDA stream per context; calls are synchronous on return.
+ * Thread-safe across contexts, not within one.  The caller owns every buffer.
+ * All arrays are float64 / int64 in C order.  There is no CPU fallback: without a CUDA
+ * device rtb_create fails with RTB_ERR_CUDA.
+ */
+#ifndef RTB_H
+#define RTB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB_ABI_VERSION 1
+
+typedef struct rtb_ctx rtb_ctx;
+
+enum rtb_status {
+    RTB_OK = 0,
+    RTB_ERR_ARG = -1,     /* bad argument (method out of range, NULL pointer, ...)   */
+    RTB_ERR_CUDA = -2,    /* CUDA runtime error, text in rtb_last_error              */
+    RTB_ERR_NOFIELD = -3, /* rtb_trace before rtb_set_field                           */
+    RTB_ERR_NOMEM = -4
+};
+
+/*
+ * A scipy RectBivariateSpline as FITPACK stores it (RT_bench.py:455-457):
+ * `tu` are the knots of the FIRST spline axis -- physical y, because the reference builds
+ * RectBivariateSpline(y, x, Z) -- `tv` the knots of the second axis (physical x), `c` the
+ * (nu-ku-1)*(nv-kv-1) coefficients, first-axis major.  Host pointers; copied.
+ */
+typedef struct {
+    const double *tu;
+    const double *tv;
+    const double *c;
+    int32_t nu, nv, ku, kv;
+} rtb_spline;
+
+/* Where caller buffers live. */
+#define RTB_PTR_HOST 0   /* host memory: the library stages H2D / D2H inside the call */
+#define RTB_PTR_DEVICE 1 /* device memory on the context's GPU (e.g. torch data_ptr()) */
+
+/* rtb_params.flags */
+#define RTB_F_INTERFACE 1u   /* op_interface: compute the Snell error metric (RT:896-919) into `errors` */
+#define RTB_F_EXACT_BASIS 2u /* evaluate B-spline bases by FITPACK's Cox-de Boor recurrence with the
+                                real knots everywhere (default: closed-form uniform-knot basis where the
+                                knots are uniform, recurrence elsewhere; differs by < 1e-13) */
+#define RTB_F_NO_TAIL_ZERO 4u /* s_ray was zero-filled by the caller: do not write the rows after a ray's
+                                 last step (np.zeros, RT:802) */
+
+typedef struct {
+    int32_t method;     /* 1..11 = op1..op11 (RT:469-764); the shim maps function objects to ids  */
+    uint32_t flags;     /* RTB_F_*                                                                  */
+    int32_t ptr_kind;   /* RTB_PTR_HOST / RTB_PTR_DEVICE for ALL array arguments of the call       */
+    int32_t out_stride; /* rows kept in s_ray: row i is stored at i/out_stride when i%out_stride==0;
+                           1 = the reference's full (max_size,6,R) array; ignored if s_ray==NULL  */
+    int64_t max_size;   /* rows of s_ray: N*divisor (fisheye) or ceil(s/step)+1 (RT:796-799)        */
+    double gamma;       /* anisotropy parameter, module global `gamma` (RT:725,758)                 */
+    double step;        /* DELTA_S                                                                  */
+    double limx_i, limx_s, limy_i, limy_s; /* box of constants() (RT:263..), strict tests RT:878    */
+    /* Optional per-ray step and max_size (length R; NULL = uniform `step`/`max_size`).  This is how
+       the DELTA_S finder batches candidates x rays into one launch (RT:1303-1318).  When given,
+       `max_size` must be the maximum of max_sizes[] and s_ray must be NULL.                       */
+    const double *steps;
+    const int64_t *max_sizes;
+} rtb_params;
+
+typedef struct {
+    double kernel_ms;   /* CUDA-event time of the integration kernel(s) on the context's stream  */
+    double total_ms;    /* CUDA-event time of the whole call incl. staging copies                 */
+    int64_t ray_steps;  /* sum over rays of d_ray[2] = executions of the loop body RT:867-879      */
+    int64_t launches;   /* kernels launched by the call                                            */
+    int64_t h2d_bytes, d2h_bytes; /* staged bytes (RTB_PTR_HOST)                                   */
+} rtb_stats;
+
+/* Create / destroy the per-GPU context (replaces the reference's process-global state). */
+int rtb_create(int device, rtb_ctx **out);
+void rtb_destroy(rtb_ctx *ctx);
+/* Launch on an existing stream (e.g. torch.cuda.current_stream().cuda_stream); NULL = own stream. */
+int rtb_set_stream(rtb_ctx *ctx, void *cuda_stream);
+const char *rtb_last_error(rtb_ctx *ctx);
+int rtb_abi_version(void);
+
+/*
+ * Upload the field: z = bilinear spline of n, gu = grd[0] (d n/d y), gv = grd[1] (d n/d x),
+ * the objects interpolacion() returns (RT:455-458).  Replaces passing `z, grd` to trazar.
+ */
+int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline *gu, const rtb_spline *gv);
+
+/*
+ * n_gradient (RT:141-156) on `n` points: out_n[i], out_gx[i] = grd[1](y,x), out_gy[i] = grd[0](y,x).
+ */
+int rtb_field_eval(rtb_ctx *ctx, int32_t ptr_kind, uint32_t flags, const double *x, const double *y,
+                   int64_t n, double *out_n, double *out_gx, double *out_gy);
+
+/*
+ * trazar (RT:766-948) for an explicit fan of R rays: ray k starts at (x0[k], y0[k]) with group
+ * angle theta0[k] (the reference takes these from constants(): theta_v, pos_x, y=-2, RT:809-813).
+ *   s_ray   (ceil(max_size/out_stride), 6, R) or NULL : x, y, p_x, p_y, T, theta per kept row (RT:802,871-875)
+ *   d_ray   (3, R)                                    : sum h, sum dist, last i (RT:888-890)
+ *   errors  (R) or NULL                               : Snell error in degrees (RTB_F_INTERFACE), else 0
+ *   last_row(6, R) or NULL                            : the last row written for each ray (row d_ray[2])
+ *   px_stats(3, R) or NULL                            : over rows 0..d_ray[2] with p_x != 0 (RT:1358):
+ *                                                       count, mean(p_x), population std(p_x)
+ * compute_times (RT:800,882) is not produced per ray -- per-ray wall time has no meaning on a GPU;
+ * the shim fills it with kernel_ms/R.
+ */
+int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0,
+              const double *y0, int64_t R, double *s_ray, double *d_ray, double *errors,
+              double *last_row, double *px_stats, rtb_stats *stats);
+
+/*
+ * Measured FP64 pipe peak (dependent-free DFMA streams on every SM), the roofline denominator
+ * of SURVEY.md 8(d); returns FLOP/s (2 per DFMA).
+ */
+int rtb_fp64_peak(rtb_ctx *ctx, double *flops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB_H */
