@@ -1,0 +1,73 @@
+"""ctypes binding of librtb.so (include/rtb.h).  There is no fallback: if the CUDA library is
+missing or no GPU is present the product path raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "librtb.so")
+
+RTB_PTR_HOST, RTB_PTR_DEVICE = 0, 1
+RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO = 1, 2, 4
+RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -3, -4
+
+# every symbol include/rtb.h declares
+EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
+           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak")
+
+
+class RtbSpline(C.Structure):
+    _fields_ = [("tu", C.c_void_p), ("tv", C.c_void_p), ("c", C.c_void_p),
+                ("nu", C.c_int32), ("nv", C.c_int32), ("ku", C.c_int32), ("kv", C.c_int32)]
+
+
+class RtbParams(C.Structure):
+    _fields_ = [("method", C.c_int32), ("flags", C.c_uint32), ("ptr_kind", C.c_int32), ("out_stride", C.c_int32),
+                ("max_size", C.c_int64), ("gamma", C.c_double), ("step", C.c_double),
+                ("limx_i", C.c_double), ("limx_s", C.c_double), ("limy_i", C.c_double), ("limy_s", C.c_double),
+                ("steps", C.c_void_p), ("max_sizes", C.c_void_p)]
+
+
+class RtbStats(C.Structure):
+    _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double), ("ray_steps", C.c_int64),
+                ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64)]
+
+
+class RtbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("librtb error %d: %s" % (code, text))
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Load librtb.so and declare the prototypes.  Raises if the extension was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("raytracing_b200: %s is missing -- build it with `make -C raytracing_b200/csrc` "
+                          "(or __graft_entry__.build()); there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, u32, i64 = C.c_void_p, C.c_int32, C.c_uint32, C.c_int64
+    lib.rtb_create.restype = C.c_int
+    lib.rtb_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.rtb_destroy.restype = None
+    lib.rtb_destroy.argtypes = [vp]
+    lib.rtb_set_stream.restype = C.c_int
+    lib.rtb_set_stream.argtypes = [vp, vp]
+    lib.rtb_last_error.restype = C.c_char_p
+    lib.rtb_last_error.argtypes = [vp]
+    lib.rtb_abi_version.restype = C.c_int
+    lib.rtb_abi_version.argtypes = []
+    lib.rtb_set_field.restype = C.c_int
+    lib.rtb_set_field.argtypes = [vp, C.POINTER(RtbSpline), C.POINTER(RtbSpline), C.POINTER(RtbSpline)]
+    lib.rtb_field_eval.restype = C.c_int
+    lib.rtb_field_eval.argtypes = [vp, i32, u32, vp, vp, i64, vp, vp, vp]
+    lib.rtb_trace.restype = C.c_int
+    lib.rtb_trace.argtypes = [vp, C.POINTER(RtbParams), vp, vp, vp, i64, vp, vp, vp, vp, vp, C.POINTER(RtbStats)]
+    lib.rtb_fp64_peak.restype = C.c_int
+    lib.rtb_fp64_peak.argtypes = [vp, C.POINTER(C.c_double)]
+    _lib = lib
+    return lib

@@ -1,0 +1,150 @@
+// field.cuh -- device evaluator of the refractive-index field n(x,y) and its gradient.
+//
+// Replaces n_gradient (RT_bench.py:141-156), i.e. three single-point calls of
+// scipy RectBivariateSpline.__call__ -> FITPACK bispev/fpbisp/fpbspl: bilinear n = z(y,x),
+// bicubic dn/dx = grd[1](y,x), dn/dy = grd[0](y,x).  The first spline axis "u" is the
+// physical y (RT_bench.py:455-457), the second "v" the physical x.
+//
+// B200 design: one thread evaluates one ray position.  The two gradient splines share
+// their knot vectors (same grid, same degree), so the bicubic basis is computed once and
+// their coefficients are stored interleaved as double2 {gu, gv}: one 16-byte gather
+// serves both splines (16 LDG.128 instead of 32 LDG.64 per step).  Knot vectors are a few
+// KB and stay in L1; coefficient tables (2-9 MB each) stay in the 126 MB L2.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtb {
+
+struct DevAxis {
+    const double *t;  // knots (device)
+    int n;            // number of knots
+    int k;            // degree
+    int off;          // interval guess: l = floor((x - t0) * inv_h) + off
+    int lo, hi;       // inclusive range of l (0-based, t[l] <= x < t[l+1]) where t[l-k+1 .. l+k] is uniform
+    double t0, inv_h; // origin and reciprocal nominal spacing of the interior knots
+    double tb, te;    // clamp range t[k], t[n-k-1]  (fpbisp: arg clamped to [tb, te])
+};
+
+struct DevField {
+    DevAxis zu, zv;    // bilinear spline of n
+    DevAxis gu_, gv_;  // shared axes of the two bicubic gradient splines
+    const double *cz;  // (zu.n-2) x (zv.n-2)
+    const double2 *cg; // interleaved {grd[0] = dn/dy, grd[1] = dn/dx}, (gu.n-4) x (gv.n-4)
+    int ncz;           // row length of cz  = zv.n - zv.k - 1
+    int ncg;           // row length of cg  = gv.n - gv.k - 1
+};
+
+// FITPACK fpbisp interval search, restated for the GPU: clamp, then find l (0-based) with
+// t[l] <= x < t[l+1], k <= l <= n-k-2.  FITPACK walks linearly from l=k; here a
+// multiply+floor guess is corrected against the real knots, which yields the same l.
+__device__ __forceinline__ int find_interval(const DevAxis &a, double &x)
+{
+    if (x < a.tb) x = a.tb;
+    if (x > a.te) x = a.te;
+    const int lmin = a.k, lmax = a.n - a.k - 2;
+    int l = __double2int_rd((x - a.t0) * a.inv_h) + a.off;
+    l = max(lmin, min(lmax, l));
+    while (l > lmin && x < __ldg(a.t + l)) --l;
+    while (l < lmax && !(x < __ldg(a.t + l + 1))) ++l;
+    return l;
+}
+
+// FITPACK fpbspl (Cox-de Boor recurrence with the real knots), K = degree; l 0-based.
+template <int K>
+__device__ __forceinline__ void basis_exact(const double *__restrict__ t, int l, double x, double *h)
+{
+    double hh[K + 1];
+    h[0] = 1.0;
+#pragma unroll
+    for (int j = 1; j <= K; ++j) {
+#pragma unroll
+        for (int i = 0; i < j; ++i) hh[i] = h[i];
+        h[0] = 0.0;
+#pragma unroll
+        for (int i = 1; i <= j; ++i) {
+            const double tli = __ldg(t + l + i);     // 1-based t(l1+i),   l1 = l+1
+            const double tlj = __ldg(t + l + i - j); // 1-based t(l1+i-j)
+            if (tli == tlj) { h[i] = 0.0; continue; }
+            const double f = hh[i - 1] / (tli - tlj);
+            h[i - 1] = h[i - 1] + f * (tli - x);
+            h[i] = f * (x - tlj);
+        }
+    }
+}
+
+// Closed-form uniform cubic B-spline basis at s = (x - t[l]) / h in [0,1).
+__device__ __forceinline__ void basis_uniform3(double s, double *w)
+{
+    const double s2 = s * s, s3 = s2 * s;
+    const double sixth = 1.0 / 6.0;
+    const double om = 1.0 - s;
+    w[0] = om * om * om * sixth;
+    w[1] = fma(s3, 0.5, fma(s2, -1.0, 2.0 / 3.0));
+    w[2] = fma(s3, -0.5, fma(s2, 0.5, fma(s, 0.5, sixth)));
+    w[3] = s3 * sixth;
+}
+
+template <bool EXACT>
+__device__ __forceinline__ int basis3(const DevAxis &a, double x, double *w)
+{
+    const int l = find_interval(a, x);
+    if (!EXACT && l >= a.lo && l <= a.hi) {
+        basis_uniform3((x - __ldg(a.t + l)) * a.inv_h, w);
+    } else {
+        basis_exact<3>(a.t, l, x, w);
+    }
+    return l;
+}
+
+template <bool EXACT>
+__device__ __forceinline__ int basis1(const DevAxis &a, double x, double *w)
+{
+    const int l = find_interval(a, x);
+    if (!EXACT && l >= a.lo && l <= a.hi) {
+        const double s = (x - __ldg(a.t + l)) * a.inv_h;
+        w[0] = 1.0 - s;
+        w[1] = s;
+    } else {
+        basis_exact<1>(a.t, l, x, w);
+    }
+    return l;
+}
+
+// n_gradient RT_bench.py:141-156: n, gx = dn/dx, gy = dn/dy at (x, y).
+template <bool EXACT>
+__device__ __forceinline__ void n_gradient(const DevField &f, double x, double y, double &n, double &gx,
+                                           double &gy)
+{
+    {
+        double wu[2], wv[2];
+        const int lu = basis1<EXACT>(f.zu, y, wu);
+        const int lv = basis1<EXACT>(f.zv, x, wv);
+        const double *c = f.cz + (size_t)(lu - 1) * f.ncz + (lv - 1);
+        const double r0 = fma(__ldg(c + 1), wv[1], __ldg(c) * wv[0]);
+        const double r1 = fma(__ldg(c + f.ncz + 1), wv[1], __ldg(c + f.ncz) * wv[0]);
+        n = fma(r1, wu[1], r0 * wu[0]);
+    }
+    {
+        double wu[4], wv[4];
+        const int lu = basis3<EXACT>(f.gu_, y, wu);
+        const int lv = basis3<EXACT>(f.gv_, x, wv);
+        const double2 *c = f.cg + (size_t)(lu - 3) * f.ncg + (lv - 3);
+        double au = 0.0, av = 0.0;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const double2 c0 = __ldg(c), c1 = __ldg(c + 1), c2 = __ldg(c + 2), c3 = __ldg(c + 3);
+            double ru = c0.x * wv[0], rv = c0.y * wv[0];
+            ru = fma(c1.x, wv[1], ru); rv = fma(c1.y, wv[1], rv);
+            ru = fma(c2.x, wv[2], ru); rv = fma(c2.y, wv[2], rv);
+            ru = fma(c3.x, wv[3], ru); rv = fma(c3.y, wv[3], rv);
+            au = fma(ru, wu[a], au);
+            av = fma(rv, wu[a], av);
+            c += f.ncg;
+        }
+        gy = au; // grd[0] = d n / d y
+        gx = av; // grd[1] = d n / d x
+    }
+}
+
+} // namespace rtb

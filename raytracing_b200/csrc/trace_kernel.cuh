@@ -1,0 +1,226 @@
+// trace_kernel.cuh -- the integrator: trazar's two nested loops (RT_bench.py:807 x 866) as
+// ONE kernel launch.  One thread owns one ray; its whole state lives in registers and the
+// thread runs the step loop itself (persistent step loop, no per-step launch).  Output is
+// the reference's ray-minor SoA s_ray[(row*6+col)*R + k] (RT_bench.py:802): for a fixed
+// row/column a warp writes 32 consecutive doubles = one 256-byte segment per store
+// instruction, so trajectory write-back is coalesced by construction; streaming (.cs)
+// stores keep the 48 B/ray-step of output from evicting the spline tables out of L2.
+#pragma once
+#include "step.cuh"
+
+namespace rtb {
+
+struct TraceArgs {
+    DevField f;
+    const double *theta0, *x0, *y0;
+    const double *steps;       // per-ray step or nullptr
+    const int64_t *max_sizes;  // per-ray max_size or nullptr
+    int64_t R;
+    int max_size;
+    int out_stride;
+    int tail_zero;
+    int interface_metric;      // unused in-kernel (kept for symmetry)
+    double step, gamma;
+    double limx_i, limx_s, limy_i, limy_s;
+    double *s_ray;             // TRAJ only
+    double *d_ray;             // (3,R)
+    double *last_row;          // (6,R) or nullptr
+    double *px_stats;          // (3,R) or nullptr
+    const int *cap_rows;       // (2,R) rows to capture (pass 2 of the Snell metric) or nullptr
+    double *cap_out;           // (4,R): x_a, y_a, x_b, y_b
+    unsigned long long *total_steps;
+};
+
+__device__ __forceinline__ void store_row(double *p, int64_t R, double x, double y, double px, double py,
+                                          double T, double ang)
+{
+    __stcs(p, x);
+    __stcs(p + R, y);
+    __stcs(p + 2 * R, px);
+    __stcs(p + 3 * R, py);
+    __stcs(p + 4 * R, T);
+    __stcs(p + 5 * R, ang);
+}
+
+template <int METHOD, bool ISO, bool TRAJ, bool EXACT>
+__global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
+{
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = r < a.R;
+    const int64_t rr = valid ? r : a.R - 1; // padded lanes shadow the last ray, never store
+    const double h = a.steps ? a.steps[rr] : a.step;
+    int M = a.max_sizes ? (int)a.max_sizes[rr] : a.max_size;
+    const double gamma = a.gamma;
+    const double g2m1 = gamma * gamma - 1.0;
+
+    int cap_a = -1, cap_b = -1;
+    if (!TRAJ && a.cap_rows) {
+        cap_a = a.cap_rows[rr];
+        cap_b = a.cap_rows[a.R + rr];
+        M = min(M, cap_b + 1); // pass 2 stops at the later captured row
+    }
+
+    // INITIAL CONDITIONS RT:809-826
+    RayState s;
+    s.x = a.x0[rr]; s.y = a.y0[rr]; s.ang = a.theta0[rr];
+    sincos(s.ang, &s.uy, &s.ux);
+    n_gradient<EXACT>(a.f, s.x, s.y, s.n, s.gx, s.gy);
+    s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
+    double px, py;
+    moments_sc<ISO>(s.n, s.coef, g2m1, s.ux, s.uy, px, py);
+    double T = 0.0, dist_sim = 0.0, dist_real = 0.0, nray_prev = s.coef * s.n;
+    double hist[3][2] = {{s.x, s.y}, {0, 0}, {0, 0}};
+
+    // p_x statistics over the non-zero entries (np.ma.masked_equal(...,0), RT:1358): shifted sums
+    double st_shift = 0.0, st_s1 = 0.0, st_s2 = 0.0;
+    int st_cnt = 0;
+    if (px != 0.0) { st_shift = px; st_cnt = 1; }
+
+    double capv[4] = {0, 0, 0, 0};
+    if (cap_a == 0) { capv[0] = s.x; capv[1] = s.y; }
+    if (cap_b == 0) { capv[2] = s.x; capv[3] = s.y; }
+
+    double *sp = nullptr;
+    int next_keep = 0; // next row index that is kept in s_ray
+    if (TRAJ) {
+        sp = a.s_ray + rr;
+        if (valid) store_row(sp, a.R, s.x, s.y, px, py, T, s.ang);
+        sp += 6 * a.R;
+        next_keep = a.out_stride;
+    }
+
+    bool alive = valid && M > 1;
+    int last_i = 0;
+    int i = 1;
+    const int Mloop = TRAJ ? a.max_size : M;
+    for (; i < Mloop; ++i) {
+        if (!__any_sync(0xffffffffu, alive)) break;
+        if (alive) {
+            double fx, fy, fang, fn, fgx, fgy;
+            if (METHOD == 7 && i < 3) { // bootstrap RT:838-864
+                const double dot = s.gx * s.ux + s.gy * s.uy;
+                const double s2 = h * h, den = 2.0 * s.n;
+                fx = (s.x + s.ux * h) + (s.gx - dot * s.ux) * s2 / den;
+                fy = (s.y + s.uy * h) + (s.gy - dot * s.uy) * s2 / den;
+                n_gradient<EXACT>(a.f, fx, fy, fn, fgx, fgy);
+                double vx, vy; // static indices keep VECTOR_LIST in registers
+                if (i == 1) {
+                    hist[1][0] = fx; hist[1][1] = fy;
+                    vx = hist[1][0] - hist[0][0]; vy = hist[1][1] - hist[0][1];
+                } else {
+                    hist[2][0] = fx; hist[2][1] = fy;
+                    vx = 3 * hist[2][0] - 4 * hist[1][0] + hist[0][0];
+                    vy = 3 * hist[2][1] - 4 * hist[1][1] + hist[0][1];
+                }
+                fang = atan2(vy, vx);
+            } else {
+                step_method<METHOD, EXACT>(a.f, s, h, gamma, g2m1, hist, fx, fy, fang, fn, fgx, fgy);
+            }
+            // store_update_results RT:783-790
+            const double dx = s.x - fx, dy = s.y - fy;
+            const double dist = sqrt(dx * dx + dy * dy);
+            dist_sim += dist;
+            dist_real += h;
+            sincos(fang, &s.uy, &s.ux);
+            s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
+            moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
+            s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
+            // RT:871-875
+            const double nray = s.coef * s.n;
+            T = T + dist * (nray_prev + nray) / 2.0;
+            nray_prev = nray;
+            last_i = i;
+            if (px != 0.0) {
+                if (st_cnt == 0) st_shift = px;
+                const double d = px - st_shift;
+                st_s1 += d;
+                st_s2 = fma(d, d, st_s2);
+                ++st_cnt;
+            }
+            if (!TRAJ) {
+                if (i == cap_a) { capv[0] = s.x; capv[1] = s.y; }
+                if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
+            }
+            // boundary test RT:878 (strict)
+            if (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i) alive = false;
+            if (i + 1 >= M) alive = false;
+            if (TRAJ && i == next_keep) {
+                store_row(sp, a.R, s.x, s.y, px, py, T, s.ang);
+                sp += 6 * a.R;
+                next_keep += a.out_stride;
+            }
+        } else if (TRAJ) {
+            if (i == next_keep) {
+                if (valid && a.tail_zero) store_row(sp, a.R, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0);
+                sp += 6 * a.R;
+                next_keep += a.out_stride;
+            }
+        }
+    }
+    if (TRAJ && a.tail_zero && valid) { // rows after the last step of every ray of this warp stay 0 (np.zeros RT:802)
+        for (; i < Mloop; ++i) {
+            if (i == next_keep) {
+                store_row(sp, a.R, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0);
+                sp += 6 * a.R;
+                next_keep += a.out_stride;
+            }
+        }
+    }
+
+    // per-ray results RT:888-890
+    if (valid) {
+        if (a.d_ray) {
+        a.d_ray[r] = dist_real;
+        a.d_ray[a.R + r] = dist_sim;
+        a.d_ray[2 * a.R + r] = (double)last_i;
+        }
+        if (a.last_row) {
+            a.last_row[r] = s.x; a.last_row[a.R + r] = s.y;
+            a.last_row[2 * a.R + r] = px; a.last_row[3 * a.R + r] = py;
+            a.last_row[4 * a.R + r] = T; a.last_row[5 * a.R + r] = s.ang;
+        }
+        if (a.px_stats) {
+            double mean = 0.0, sd = 0.0;
+            if (st_cnt > 0) {
+                const double m1 = st_s1 / st_cnt;
+                mean = st_shift + m1;
+                const double var = st_s2 / st_cnt - m1 * m1;
+                sd = var > 0.0 ? sqrt(var) : 0.0;
+            }
+            a.px_stats[r] = (double)st_cnt;
+            a.px_stats[a.R + r] = mean;
+            a.px_stats[2 * a.R + r] = sd;
+        }
+        if (!TRAJ && a.cap_out) {
+            a.cap_out[r] = capv[0]; a.cap_out[a.R + r] = capv[1];
+            a.cap_out[2 * a.R + r] = capv[2]; a.cap_out[3 * a.R + r] = capv[3];
+        }
+    }
+    // ray-step count = sum of d_ray[2]; one atomic per warp
+    if (a.total_steps) {
+        unsigned v = valid ? (unsigned)last_i : 0u;
+        v = __reduce_add_sync(0xffffffffu, v);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(a.total_steps, (unsigned long long)v);
+    }
+}
+
+// Host-side launcher, one per METHOD (instantiated in trace_inst.cu).
+typedef cudaError_t (*launch_fn)(const TraceArgs &, bool iso, bool traj, bool exact, int block, cudaStream_t);
+
+template <int METHOD>
+cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
+{
+    const unsigned grid = (unsigned)((a.R + block - 1) / block);
+#define RTB_L(I, T, E) trace_kernel<METHOD, I, T, E><<<grid, block, 0, st>>>(a)
+    if (iso) {
+        if (traj) { if (exact) RTB_L(true, true, true); else RTB_L(true, true, false); }
+        else      { if (exact) RTB_L(true, false, true); else RTB_L(true, false, false); }
+    } else {
+        if (traj) { if (exact) RTB_L(false, true, true); else RTB_L(false, true, false); }
+        else      { if (exact) RTB_L(false, false, true); else RTB_L(false, false, false); }
+    }
+#undef RTB_L
+    return cudaGetLastError();
+}
+
+} // namespace rtb

@@ -1,0 +1,185 @@
+"""Host-side mirror of RT_bench.py's hot-path interface on top of librtb.so.
+
+`Engine` owns one C-ABI context (one GPU).  The module-level `trazar`, `search_delta`,
+`n_gradient` keep the reference's names, argument meaning and return values
+(RT_bench.py:766-948, 950-958, 141-156) and run on the GPU; nothing here computes the path on
+the CPU.  PyTorch is used only to hand device memory / streams to the library.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _cabi
+from . import constants as K
+from .field import build_field, spline_arrays
+
+
+def method_id(selected_func):
+    """Map op1..op11 given as int, "op6"/"6", or the reference's function object (by __name__,
+    trazar compares `selected_func == op7`, RT_bench.py:833) to 1..11."""
+    if callable(selected_func):
+        selected_func = getattr(selected_func, "__name__", "")
+    s = str(selected_func).strip().lower()
+    if s.startswith("op"):
+        s = s[2:]
+    try:
+        m = int(s)
+    except ValueError:
+        raise ValueError("unknown step method %r (expected op1..op11)" % (selected_func,))
+    if not 1 <= m <= 11:
+        raise ValueError("step method must be op1..op11, got %r" % (selected_func,))
+    return m
+
+
+def max_size_for(user_choice, step, divisor):
+    """RT_bench.py:796-799."""
+    uc = K.scenario_id(user_choice)
+    if uc == "2":
+        return int(K.N * divisor)
+    return int(np.ceil(K.constants(uc)[4] / step) + 1)
+
+
+def default_fan(user_choice):
+    """(theta0, x0, y0) of the scenario's default fan, RT_bench.py:809-813."""
+    uc = K.scenario_id(user_choice)
+    _g, R, theta_v, pos_x = K.constants(uc)[:4]
+    theta0 = np.asarray(theta_v[:R], dtype=np.float64)
+    if uc == "2":
+        return theta0, np.full(R, float(pos_x[0])), np.full(R, float(pos_x[1]))
+    return theta0, np.asarray(pos_x, dtype=np.float64), np.full(R, -2.0)
+
+
+class TraceResult(dict):
+    """dict with attribute access: s_ray, d_ray, errors, last_row, px_stats, stats."""
+    __getattr__ = dict.__getitem__
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+class Engine:
+    """One librtb context on one GPU."""
+
+    def __init__(self, device=0):
+        self._lib = _cabi.load()
+        self._ctx = C.c_void_p()
+        rc = self._lib.rtb_create(int(device), C.byref(self._ctx))
+        if rc != 0:
+            raise _cabi.RtbError(rc, "rtb_create(device=%d) failed: no usable CUDA device "
+                                     "(raytracing_b200 has no CPU fallback)" % device)
+        self.device = int(device)
+        self._field_key = None
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx:
+            self._lib.rtb_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise _cabi.RtbError(rc, self._lib.rtb_last_error(self._ctx).decode())
+
+    def use_torch_stream(self):
+        """Launch on torch's current stream so torch.cuda.Event timing brackets the kernels."""
+        import torch
+        self._check(self._lib.rtb_set_stream(self._ctx, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+
+    def set_field(self, z, grd):
+        """Upload z (bilinear n) and grd = (dn/dy spline, dn/dx spline) as interpolacion() returns
+        them (RT_bench.py:455-458); scipy objects or (tu, tv, c, ku, kv) tuples."""
+        key = (id(z), id(grd[0]), id(grd[1]))
+        if key == self._field_key:
+            return
+        arrs = [spline_arrays(s) for s in (z, grd[0], grd[1])]
+        structs = [_cabi.RtbSpline(a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data,
+                                   a[0].size, a[1].size, a[3], a[4]) for a in arrs]
+        self._check(self._lib.rtb_set_field(self._ctx, *[C.byref(s) for s in structs]))
+        self._field_key = key
+        self._keep = (z, grd)  # keep ids alive so the cache key stays valid
+
+    def fp64_peak(self):
+        v = C.c_double()
+        self._check(self._lib.rtb_fp64_peak(self._ctx, C.byref(v)))
+        return v.value
+
+    def n_gradient(self, x, y, exact=False):
+        """Batched n_gradient (RT_bench.py:141-156): returns n, gx, gy arrays."""
+        x = np.ascontiguousarray(x, dtype=np.float64).ravel()
+        y = np.ascontiguousarray(y, dtype=np.float64).ravel()
+        n, gx, gy = (np.empty_like(x) for _ in range(3))
+        flags = _cabi.RTB_F_EXACT_BASIS if exact else 0
+        self._check(self._lib.rtb_field_eval(self._ctx, _cabi.RTB_PTR_HOST, flags, x.ctypes.data, y.ctypes.data,
+                                             x.size, n.ctypes.data, gx.ctypes.data, gy.ctypes.data))
+        return n, gx, gy
+
+    def trace(self, method, theta0, x0, y0, step, max_size, gamma, box, interface=False, full=True,
+              out_stride=1, want_last_row=True, want_px_stats=False, want_errors=None, exact=False,
+              steps=None, max_sizes=None, out=None, tail_zero=True):
+        """trazar's integration for an explicit fan.
+
+        Inputs are numpy arrays (host pointers, staged inside the call) or torch CUDA tensors
+        (device pointers; outputs are then torch tensors too).  `out` may supply preallocated
+        outputs by name.  Returns TraceResult.
+        """
+        m = method_id(method)
+        dev = _is_torch(theta0)
+        out = dict(out or {})
+        if want_errors is None:
+            want_errors = bool(interface)
+        if dev:
+            import torch
+            R = theta0.numel()
+            f64 = dict(dtype=torch.float64, device=theta0.device)
+            def prep(a):
+                if not _is_torch(a):
+                    a = torch.as_tensor(np.broadcast_to(np.asarray(a, dtype=np.float64), (R,)).copy()).to(theta0.device)
+                assert a.dtype == torch.float64 and a.is_contiguous() and a.numel() == R
+                return a
+            empty = lambda *shape: torch.empty(*shape, **f64)
+            ptr = lambda a: C.c_void_p(a.data_ptr()) if a is not None else None
+        else:
+            theta0 = np.ascontiguousarray(theta0, dtype=np.float64).ravel()
+            R = theta0.size
+            prep = lambda a: np.ascontiguousarray(np.broadcast_to(np.asarray(a, dtype=np.float64), (R,)))
+            empty = lambda *shape: np.empty(shape, dtype=np.float64)
+            ptr = lambda a: C.c_void_p(a.ctypes.data) if a is not None else None
+        theta0, x0, y0 = prep(theta0), prep(x0), prep(y0)
+        max_size = int(max_size)
+        rows = (max_size + out_stride - 1) // out_stride
+        s_ray = out.get("s_ray", empty(rows, 6, R) if full else None)
+        d_ray = out.get("d_ray", empty(3, R))
+        errors = out.get("errors", empty(R) if want_errors else None)
+        last_row = out.get("last_row", empty(6, R) if want_last_row else None)
+        px_stats = out.get("px_stats", empty(3, R) if want_px_stats else None)
+        flags = (_cabi.RTB_F_INTERFACE if interface else 0) | (_cabi.RTB_F_EXACT_BASIS if exact else 0) | \
+                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO)
+        steps_a = max_sizes_a = None
+        if steps is not None:
+            if dev:
+                steps_a = steps
+                max_sizes_a = max_sizes
+                sp, mp = ptr(steps_a), ptr(max_sizes_a)
+            else:
+                steps_a = np.ascontiguousarray(steps, dtype=np.float64)
+                max_sizes_a = np.ascontiguousarray(max_sizes, dtype=np.int64)
+                sp, mp = ptr(steps_a), ptr(max_sizes_a)
+        else:
+            sp = mp = None
+        p = _cabi.RtbParams(m, flags, _cabi.RTB_PTR_DEVICE if dev else _cabi.RTB_PTR_HOST, int(out_stride),
+                            max_size, float(gamma), float(step if step is not None else 0.0),
+                            float(box[0]), float(box[1]), float(box[2]), float(box[3]), sp, mp)
+        stats = _cabi.RtbStats()
+        self._check(self._lib.rtb_trace(self._ctx, C.byref(p), ptr(theta0), ptr(x0), ptr(y0), R, ptr(s_ray),
+                                        ptr(d_ray), ptr(errors), ptr(last_row), ptr(px_stats), C.byref(stats)))
+        return TraceResult(s_ray=s_ray, d_ray=d_ray, errors=errors, last_row=last_row, px_stats=px_stats,
+                           stats=dict(kernel_ms=stats.kernel_ms, total_ms=stats.total_ms, ray_steps=stats.ray_steps,
+                                      launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes))
