@@ -25,6 +25,27 @@
 
 #define RTO_PI 3.141592653589793
 
+/*
+ * Sensitivity probe (tests only): when enabled, every sin/cos result is moved by +-1 ulp with
+ * probability 1/2, i.e. replaced by the answer another correct (<= 1 ulp) libm could give.  The
+ * spread of the outputs under this noise is the reference ALGORITHM's own conditioning and
+ * bounds the parity any independent implementation (different libm, FMA contraction) can reach.
+ */
+static int g_noise = 0;
+static _Thread_local uint64_t g_rng = 0x9E3779B97F4A7C15ull;
+void rto_set_trig_noise(int seed) { g_noise = seed; }
+static inline double noisy(double r)
+{
+    if (!g_noise) return r;
+    g_rng ^= g_rng << 13; g_rng ^= g_rng >> 7; g_rng ^= g_rng << 17;
+    unsigned b = (unsigned)(g_rng >> 33) & 3u;
+    if (b == 0) return nextafter(r, INFINITY);
+    if (b == 1) return nextafter(r, -INFINITY);
+    return r;
+}
+static inline double rsin(double x) { return noisy(sin(x)); }
+static inline double rcos(double x) { return noisy(cos(x)); }
+
 typedef struct {
     const double *tu; /* knots of the first spline axis (physical y, RT:455-457) */
     const double *tv; /* knots of the second spline axis (physical x)            */
@@ -113,7 +134,7 @@ static void n_gradient(const field_t *f, double x, double y, double *n, double *
 /* anisotropy RT:118-119 */
 static double anisotropy(double theta, double gamma)
 {
-    double a = gamma * sin(theta), b = cos(theta);
+    double a = gamma * rsin(theta), b = rcos(theta);
     return sqrt(a * a + b * b);
 }
 
@@ -159,11 +180,11 @@ static int curvature_t(double ang, double gx, double gy, double ux, double uy, d
     }
     double d = curv * step;
     if (gx * uy - gy * ux > 0) {
-        *fx = x + (sin(ang) - sin(ang - d)) / curv;
-        *fy = y + (cos(ang - d) - cos(ang)) / curv;
+        *fx = x + (rsin(ang) - rsin(ang - d)) / curv;
+        *fy = y + (rcos(ang - d) - rcos(ang)) / curv;
     } else {
-        *fx = x + (sin(ang + d) - sin(ang)) / curv;
-        *fy = y + (-cos(ang + d) + cos(ang)) / curv;
+        *fx = x + (rsin(ang + d) - rsin(ang)) / curv;
+        *fy = y + (-rcos(ang + d) + rcos(ang)) / curv;
     }
     return 1;
 }
@@ -172,15 +193,15 @@ static int curvature_t(double ang, double gx, double gy, double ux, double uy, d
 static double tfinal_2o(double ang, double step, double n0, double n1, double gx0, double gy0,
                         double gx1, double gy1)
 {
-    double k1 = step * (cos(ang) * gy0 - sin(ang) * gx0) / n0;
-    double k2 = step * (cos(ang + k1) * gy1 - sin(ang + k1) * gx1) / n1;
+    double k1 = step * (rcos(ang) * gy0 - rsin(ang) * gx0) / n0;
+    double k2 = step * (rcos(ang + k1) * gy1 - rsin(ang + k1) * gx1) / n1;
     return ang + (k1 + k2) / 2.0;
 }
 
 /* theta_cost_t RT:393-407 */
 static double theta_cost_t(double n0, double ang, double gx0, double gy0, double gx1, double gy1, double step)
 {
-    return atan2(n0 * sin(ang) + impulse_t(gy0, gy1, step), n0 * cos(ang) + impulse_t(gx0, gx1, step));
+    return atan2(n0 * rsin(ang) + impulse_t(gy0, gy1, step), n0 * rcos(ang) + impulse_t(gx0, gx1, step));
 }
 
 typedef struct {
@@ -192,11 +213,11 @@ typedef struct {
 static double cost(const cost_t *c, double th)
 {
     if (!c->aniso) {
-        double a = c->n1 * cos(th) - c->n0 * c->ux - impulse_t(c->gx0, c->gx1, c->step);
-        double b = c->n1 * sin(th) - c->n0 * c->uy - impulse_t(c->gy0, c->gy1, c->step);
+        double a = c->n1 * rcos(th) - c->n0 * c->ux - impulse_t(c->gx0, c->gx1, c->step);
+        double b = c->n1 * rsin(th) - c->n0 * c->uy - impulse_t(c->gy0, c->gy1, c->step);
         return a * a + b * b;
     }
-    double st = sin(th), ct = cos(th);
+    double st = rsin(th), ct = rcos(th);
     double a = moment(c->n1, th, c->gamma, ct, -(st * st)) - c->mi_x -
                impulse_t(c->coef_i * c->gx0, anisotropy(th, c->gamma) * c->gx1, c->step);
     double b = moment(c->n1, th, c->gamma, st, ct * ct) - c->mi_y -
@@ -267,7 +288,7 @@ static double snell_error(double theta0, const double *px, const double *py, int
     double angreal;
     if (theta0 < RTO_PI / 4) angreal = 90 - 180 * theta0 / RTO_PI;
     else if (theta0 == RTO_PI / 4) angreal = 0;
-    else angreal = 180 * asin(sqrt(2.0) * sin(RTO_PI / 2 - theta0)) / RTO_PI;
+    else angreal = 180 * asin(sqrt(2.0) * rsin(RTO_PI / 2 - theta0)) / RTO_PI;
     int64_t ib = (int64_t)(9.5 * (double)i / 10);
     int64_t ia = (int64_t)((double)(9 * i) / 10);
     double distx = px[ib] - px[ia], disty = py[ib] - py[ia];
@@ -301,11 +322,12 @@ int64_t rto_trace(const rto_params *p, const rto_spline *z, const rto_spline *gu
             px = (double *)malloc(sizeof(double) * (size_t)M);
             py = (double *)malloc(sizeof(double) * (size_t)M);
         }
+        g_rng = 0x9E3779B97F4A7C15ull ^ ((uint64_t)(g_noise + 1) * 0xD1B54A32D192ED03ull) ^ ((uint64_t)k << 20);
         state_t s;
         double hist[3][2] = {{0, 0}, {0, 0}, {0, 0}};
         double row[6];
         s.x = x0[k]; s.y = y0[k]; s.ang = theta0[k];
-        s.ux = cos(s.ang); s.uy = sin(s.ang);
+        s.ux = rcos(s.ang); s.uy = rsin(s.ang);
         n_gradient(&f, s.x, s.y, &s.n, &s.gx, &s.gy);
         s.coef = anisotropy(s.ang, p->gamma);
         double mx, my;
@@ -335,7 +357,7 @@ int64_t rto_trace(const rto_params *p, const rto_spline *z, const rto_spline *gu
             double dist = sqrt(dx * dx + dy * dy);
             dist_sim += dist;
             dist_real += p->step;
-            s.ux = cos(fang); s.uy = sin(fang);
+            s.ux = rcos(fang); s.uy = rsin(fang);
             s.coef = anisotropy(fang, p->gamma);
             moments(fang, fn, s.ux, s.uy, p->gamma, &mx, &my);
             s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;

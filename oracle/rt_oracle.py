@@ -45,6 +45,8 @@ def lib():
         _lib.rto_trace.argtypes = [C.POINTER(Params)] + [C.POINTER(Spline)] * 3 + [C.c_void_p] * 3 + \
             [C.c_int64] + [C.c_void_p] * 4 + [C.c_int]
         _lib.rto_max_threads.restype = C.c_int
+        _lib.rto_set_trig_noise.restype = None
+        _lib.rto_set_trig_noise.argtypes = [C.c_int]
     return _lib
 
 
@@ -112,3 +114,9 @@ def trace(method, z, grd, step, max_size, gamma, box, is_interface, theta0, x0, 
 
 def max_threads():
     return int(lib().rto_max_threads())
+
+
+def set_trig_noise(seed):
+    """0 = off (faithful oracle); >0 = every sin/cos result moved by +-1 ulp with probability 1/2
+    (sensitivity probe of the reference algorithm, see rt_oracle.c)."""
+    lib().rto_set_trig_noise(int(seed))

@@ -1,0 +1,175 @@
+"""Generate the golden fixtures in tests/golden/ from the UNMODIFIED reference.
+
+Runs only in the build container (needs /root/reference); the fixtures are committed so the
+tests run anywhere.  Usage:  python tests/golden/gen_golden.py [traj|field|sweep|sens|all]
+
+  ref_traj.npz    trazar outputs of every (scenario, method) on the default fans (d_ray, errors,
+                  strided s_ray rows, last row per ray) and on slices of the synthetic fans
+  ref_field.npz   n_gradient at random points and next to knots, per scenario
+  ref_sweep.npz   search_delta metrics over the DELTA_S sweep + find_index result (RT:1303-1385)
+  sensitivity.json  the reference algorithm's response to +-1 ulp sin/cos noise (oracle probe,
+                  cross-checked against the same probe on the real reference for a few cases)
+"""
+import json
+import os
+import sys
+import warnings
+from multiprocessing import Pool
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+warnings.filterwarnings("ignore")
+
+from oracle import ref_loader as L  # noqa: E402
+
+SCEN = {"1": list(range(1, 10)), "2": list(range(1, 10)), "3": list(range(1, 10)), "4": [10, 11]}
+ROWS_KEPT = 48
+
+
+def synthetic_fans():
+    """Slices of the benchmark fans (raytracing_b200.fans.make_fan) small enough for the reference."""
+    from raytracing_b200.fans import make_fan
+    out = {}
+    for uc, R, idx in (("2", 1 << 20, [0, 1, 349525, 524288, 1048574, 1048575]),
+                       ("3", 1 << 26, [0, 7, 22369621, 44739242, 67108863]),
+                       ("4", 1 << 24, [3, 8388608, 16777215])):
+        th = np.concatenate([make_fan(uc, R, i, i + 1)[0] for i in idx])
+        out[uc] = (R, np.array(idx), th)
+    return out
+
+
+def _trace_task(args):
+    uc, m, fan_theta, tag = args
+    RT = L.load_reference()
+    fan = None if fan_theta is None else dict(theta_v=fan_theta, ray_count=len(fan_theta))
+    z, grd = L.setup_scenario(RT, uc, fan)
+    s, d, _ct, e = RT.trazar(L.method(RT, m), z, grd, False, RT.DELTA_S, RT.DELTA_S_DIVISOR_FISHEYE + 1, uc)
+    M, _, R = s.shape
+    stride = max(1, M // ROWS_KEPT)
+    last = np.stack([s[int(d[2, k]), :, k] for k in range(R)], axis=1)
+    key = "%s_s%s_op%d" % (tag, uc, m)
+    return key, dict(d_ray=d, errors=e, rows=s[::stride].copy(), stride=np.int64(stride), M=np.int64(M),
+                     last_row=last, theta0=np.asarray(RT.theta_v[:R], dtype=np.float64),
+                     px_sum=s[:, 2, :].sum(axis=0), T_last=last[4])
+
+
+def gen_traj():
+    tasks = [(uc, m, None, "default") for uc, ms in SCEN.items() for m in ms]
+    for uc, (_R, _idx, th) in synthetic_fans().items():
+        tasks += [(uc, m, th, "synth") for m in SCEN[uc]]
+    tasks.sort(key=lambda t: -(100 if t[1] >= 10 else 10 if t[1] in (5, 9) else 1) * (42 if t[0] == "1" else 31))
+    flat = {}
+    with Pool(8) as pool:
+        for key, d in pool.imap_unordered(_trace_task, tasks):
+            print("traj", key, d["d_ray"][2].sum(), flush=True)
+            for k, v in d.items():
+                flat[key + "/" + k] = v
+    for uc, (R, idx, _th) in synthetic_fans().items():
+        flat["synth_s%s/R" % uc] = np.int64(R)
+        flat["synth_s%s/idx" % uc] = idx
+    np.savez_compressed(os.path.join(HERE, "ref_traj.npz"), **flat)
+
+
+def gen_field():
+    flat = {}
+    for uc in "123":
+        RT = L.load_reference()
+        z, grd = L.setup_scenario(RT, uc)
+        rng = np.random.default_rng(int(uc))
+        n = 600
+        x = rng.uniform(RT.limx_i - 0.2, RT.limx_s + 0.2, n)
+        y = rng.uniform(RT.limy_i - 0.2, RT.limy_s + 0.2, n)
+        tu, tv, _ = grd[0].tck
+        # on and right next to knots, and clamped points outside the grid
+        ku = rng.choice(tu[4:-4], 60); kv = rng.choice(tv[4:-4], 60)
+        x = np.concatenate([x, kv, np.nextafter(kv, -np.inf), np.nextafter(kv, np.inf), [tv[0] - 1, tv[-1] + 1, tv[0], tv[-1]]])
+        y = np.concatenate([y, ku, np.nextafter(ku, np.inf), np.nextafter(ku, -np.inf), [tu[0] - 1, tu[-1] + 1, tu[-1], tu[0]]])
+        res = [RT.n_gradient(np.array([a, b]), grd, z) for a, b in zip(x, y)]
+        flat["s%s/x" % uc] = x; flat["s%s/y" % uc] = y
+        flat["s%s/n" % uc] = np.array([r[0] for r in res])
+        flat["s%s/g" % uc] = np.array([r[1] for r in res])
+        print("field", uc, len(x), flush=True)
+    np.savez_compressed(os.path.join(HERE, "ref_field.npz"), **flat)
+
+
+def _sweep_task(args):
+    uc, m, step, div = args
+    RT = L.load_reference()
+    z, grd = L.setup_scenario(RT, uc)
+    r = RT.search_delta(L.method(RT, m), z, grd, step, div + 1, uc)
+    if uc in "34":  # reduce the p_x matrix exactly as RT:1354-1360 does
+        cvs = np.zeros(RT.ray_count - 2)
+        for i in range(1, RT.ray_count - 1):
+            masked = np.ma.masked_equal(r[:, i], 0).compressed()
+            cvs[i - 1] = 100 * np.std(masked) / np.mean(masked)
+        r = np.mean(cvs)
+    return r
+
+
+def gen_sweep():
+    from raytracing_b200 import api
+    flat = {}
+    with Pool(8) as pool:
+        for uc, m in (("2", 6), ("2", 1), ("3", 6), ("3", 4), ("1", 6), ("4", 11)):
+            divisors, options, max_dev = api.sweep_candidates(uc)
+            if uc == "4":  # 2 ms/step in the reference: keep every 8th candidate
+                divisors, options = divisors[::8], options[::8]
+            res = pool.map(_sweep_task, [(uc, m, s, d) for s, d in zip(options, divisors)])
+            key = "s%s_op%d" % (uc, m)
+            if uc == "1":
+                prom, mx = [r[0] for r in res], [r[1] for r in res]
+                idx = api.find_index_interface(prom, mx, max_dev)
+                flat[key + "/mean"] = np.array(prom); flat[key + "/max"] = np.array(mx)
+            else:
+                idx = (api.find_index_fisheye if uc == "2" else api.find_index_vert)(res, max_dev)
+                flat[key + "/metric"] = np.array(res)
+            flat[key + "/index"] = np.int64(-1 if idx is None else idx)
+            flat[key + "/divisors"] = divisors
+            print("sweep", key, "index", idx, flush=True)
+    np.savez_compressed(os.path.join(HERE, "ref_sweep.npz"), **flat)
+
+
+def gen_sens():
+    """Oracle noise probe on the default fans: per (scenario, method) the max deviation of positions,
+    of all s_ray columns, of the Snell errors, and which rays change their step count."""
+    from oracle import rt_oracle as O
+    import raytracing_b200 as rt
+    out = {}
+    for uc, ms in SCEN.items():
+        z, grd = rt.build_field(uc)
+        c = rt.scenario_constants(uc)
+        theta0, x0, y0 = rt.default_fan(uc)
+        M = rt.max_size_for(uc, rt.DELTA_S, 91)
+        for m in ms:
+            O.set_trig_noise(0)
+            base = O.trace(m, z, grd, rt.DELTA_S, M, c[0], c[5:9], uc == "1", theta0, x0, y0, nthreads=8)
+            dev = dict(pos=0.0, all=0.0, d_ray=0.0, err=0.0, unstable_rays=[])
+            for seed in (1, 2, 3):
+                O.set_trig_noise(seed)
+                r = O.trace(m, z, grd, rt.DELTA_S, M, c[0], c[5:9], uc == "1", theta0, x0, y0, nthreads=8)
+                same = base["d_ray"][2] == r["d_ray"][2]
+                dev["unstable_rays"] = sorted(set(dev["unstable_rays"]) | set(np.nonzero(~same)[0].tolist()))
+                ds = np.abs(base["s_ray"] - r["s_ray"])[:, :, same]
+                dev["pos"] = max(dev["pos"], float(ds[:, 0:2].max()))
+                dev["all"] = max(dev["all"], float(ds.max()))
+                dev["d_ray"] = max(dev["d_ray"], float(np.abs(base["d_ray"][:2] - r["d_ray"][:2])[:, same].max()))
+                dev["err"] = max(dev["err"], float(np.abs(base["errors"] - r["errors"])[same].max()))
+            O.set_trig_noise(0)
+            out["s%s_op%d" % (uc, m)] = dev
+            print("sens", uc, m, dev, flush=True)
+    json.dump(out, open(os.path.join(HERE, "sensitivity.json"), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    what = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if what in ("sens", "all"):
+        gen_sens()
+    if what in ("field", "all"):
+        gen_field()
+    if what in ("traj", "all"):
+        gen_traj()
+    if what in ("sweep", "all"):
+        gen_sweep()
