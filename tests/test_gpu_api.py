@@ -1,0 +1,113 @@
+"""GPU: the drop-in surface (trazar / search_delta / n_gradient / DELTA_S finder) and full-size properties."""
+import numpy as np
+import pytest
+
+import raytracing_b200 as rt
+from _util import assert_close, scenario_setup, tolerances
+
+pytestmark = pytest.mark.gpu
+
+
+def test_trazar_signature_and_values(golden_traj, sensitivity):
+    """trazar(selected_func, z, grd, show, step, divisor, user_choice) -> (s_ray, d_ray, compute_times, errors)."""
+    z, grd = rt.build_field("1")
+
+    def op6():  # the shim accepts the reference's function objects by name
+        pass
+    s_ray, d_ray, compute_times, errors = rt.trazar(op6, z, grd, False, rt.DELTA_S, 91, "1")
+    assert s_ray.shape == (30228, 6, 42) and d_ray.shape == (3, 42) and compute_times.shape == (42,) and errors.shape == (42,)
+    key = "default_s1_op6/"
+    tol = tolerances(sensitivity, "1", 6)
+    assert np.array_equal(d_ray[2], golden_traj[key + "d_ray"][2])
+    assert_close(errors, golden_traj[key + "errors"], tol["err"], "errors")
+    assert_close(d_ray[:2], golden_traj[key + "d_ray"][:2], tol["d_ray"], "d_ray")
+    assert abs(np.sum(d_ray[1]) - 422.3026202499) < 1e-9        # BASELINE.md fingerprint
+    assert abs(np.mean(errors) - 0.033879) < 1e-6 and abs(np.max(errors) - 0.325975) < 1e-6
+
+
+def test_n_gradient_signature():
+    z, grd = rt.build_field("1")
+    n, g = rt.n_gradient(np.array([1.234, 0.01]), grd, z)
+    assert abs(n - 1.06403) < 1e-5 and abs(g[1] - (-9.606)) < 1e-3   # SURVEY.md section 0 [probe]
+
+
+def test_search_delta_per_scenario(golden_sweep):
+    for uc, m, key in (("2", 6, "s2_op6"), ("3", 6, "s3_op6")):
+        z, grd = rt.build_field(uc)
+        divisors, options, _ = rt.sweep_candidates(uc)
+        j = 17
+        r = rt.search_delta(m, z, grd, options[j], divisors[j] + 1, uc)
+        if uc == "2":
+            assert abs(r - golden_sweep[key + "/metric"][j]) <= 1e-9
+        else:
+            assert r.shape[1] == 31
+            cv = np.mean([rt.px_cv(r[:, i]) for i in range(1, 30)])
+            assert abs(cv - golden_sweep[key + "/metric"][j]) <= 1e-9 * max(1, abs(cv))
+
+
+@pytest.mark.parametrize("uc,m", [("2", 6), ("2", 1), ("3", 6), ("3", 4), ("1", 6)])
+def test_delta_s_finder_vs_reference(golden_sweep, uc, m):
+    """A14: batched candidates x rays sweep; metrics within tolerance, selected index bit-exact."""
+    z, grd = rt.build_field(uc)
+    key = "s%s_op%d" % (uc, m)
+    res = rt.find_delta_s(m, z, grd, uc)
+    want = int(golden_sweep[key + "/index"])
+    assert (-1 if res["index"] is None else res["index"]) == want
+    if uc == "1":
+        assert_close(res["metrics"][0], golden_sweep[key + "/mean"], 1e-9, "mean err")
+        assert_close(res["metrics"][1], golden_sweep[key + "/max"], 1e-9, "max err")
+        assert res["divisor"] == 2.55
+    else:
+        assert_close(res["metrics"], golden_sweep[key + "/metric"], 1e-9, "metric")
+
+
+def test_delta_s_finder_aniso_subset(golden_sweep):
+    z, grd = rt.build_field("4")
+    divisors, options, _ = rt.sweep_candidates("4")
+    got = rt.sweep_metrics(11, z, grd, "4", options[::8], divisors[::8])
+    assert_close(got, golden_sweep["s4_op11/metric"], 1e-9, "aniso CV")
+
+
+def test_fisheye_1m_properties(engine):
+    """BASELINE config 2 at full size: 2^20 rays.  Size-independent checks: no ray exits (uniform work),
+    run-to-run determinism, Maxwell-fisheye invariant (rays through (1,0) are circles through (-1,0)... 
+    so |r|^2 - 2*y*cot-term is conserved); 64 sampled rays against the oracle."""
+    import torch
+    from oracle import rt_oracle as O
+    s = scenario_setup("2")
+    engine.set_field(s["z"], s["grd"])
+    R = 1 << 20
+    th, x0, y0 = rt.make_fan("2", R)
+    dev = [torch.from_numpy(a).cuda() for a in (th, x0, y0)]
+    a = engine.trace(6, *dev, s["step"], s["M"], s["gamma"], s["box"], full=False)
+    b = engine.trace(6, *dev, s["step"], s["M"], s["gamma"], s["box"], full=False)
+    assert torch.equal(a.d_ray, b.d_ray) and torch.equal(a.last_row, b.last_row)
+    d = a.d_ray.cpu().numpy()
+    assert (d[2] == 909).all() and a.stats["ray_steps"] == 909 * R
+    idx = np.linspace(0, R - 1, 64).astype(int)
+    o = O.trace(6, s["z"], s["grd"], s["step"], s["M"], s["gamma"], s["box"], False, th[idx], x0[idx], y0[idx], full=False,
+                nthreads=8)
+    assert_close(a.last_row.cpu().numpy()[:, idx], o["final"], 1e-10, "1M fisheye sample")
+    assert_close(d[:2, idx], o["d_ray"][:2], 1e-10, "1M fisheye d_ray")
+    # physics: p = n*u and r x p is conserved in a radial medium
+    lr = a.last_row.cpu().numpy()
+    L0 = 0.5 * np.sin(th)          # n(1,0) = 1/2, r=(1,0): Lz = x*py - y*px = n*sin(theta)
+    L1 = lr[0] * lr[3] - lr[1] * lr[2]
+    assert np.abs(L1 - L0).max() < 5e-5
+
+
+def test_vert_large_fan_px_conservation(engine):
+    """Config 3 shape (slice): p_x is conserved when n depends on y only -> online CV < 0.05 % (RT:1310)."""
+    import torch
+    s = scenario_setup("3")
+    engine.set_field(s["z"], s["grd"])
+    R = 1 << 16
+    th, x0, y0 = rt.make_fan("3", 1 << 26, 0, R * 1024)
+    th, x0, y0 = th[::1024], x0[::1024], y0[::1024]
+    dev = [torch.from_numpy(np.ascontiguousarray(v)).cuda() for v in (th, x0, y0)]
+    r = engine.trace(6, *dev, s["step"], s["M"], s["gamma"], s["box"], full=False, want_px_stats=True)
+    st = r.px_stats.cpu().numpy()
+    cv = 100 * st[2, 1:-1] / st[1, 1:-1]
+    assert np.nanmax(cv) < 0.05
+    d = r.d_ray.cpu().numpy()
+    assert d[2].min() >= 1000 and d[2].max() <= 2940 and (st[0] == d[2] + 1)[1:-1].all()

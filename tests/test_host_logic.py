@@ -1,0 +1,99 @@
+"""CPU: host-side mirror of the reference's selection surface (constants, tables, rules)."""
+import numpy as np
+import pytest
+
+import raytracing_b200 as rt
+from raytracing_b200 import api, constants as K
+
+
+def test_constants_match_reference_values():
+    # SURVEY.md 8 [probe] values of RT_bench.py:59-97
+    assert K.SIGMA == 0.05293304824724534
+    assert K.DELTA == 0.017644349415748446
+    assert K.DELTA_S == 0.002646652412362267
+    assert K.GOLD_TOL == 1.4901161193847656e-08
+    assert K.GOLD_RATIO == (np.sqrt(5) - 1) / 2
+
+
+def test_scenario_table():
+    c1 = rt.scenario_constants("1")
+    assert c1[1] == 42 and len(c1[2]) == 43 and c1[4] == 80 and c1[5:9] == (-2, 20, -2, 4)
+    c2 = rt.scenario_constants("fisheye")
+    assert c2[1] == 1 and c2[4] == 10 * 2 * np.pi and tuple(c2[3]) == (1, 0)
+    assert rt.scenario_constants("4")[0] == 3 and rt.scenario_constants("3")[0] == 1
+    with pytest.raises(ValueError):
+        rt.scenario_constants("5")
+
+
+def test_max_size_and_methods():
+    assert rt.max_size_for("1", K.DELTA_S, 91) == 30228
+    assert rt.max_size_for("2", K.DELTA_S, 91) == 910
+    assert rt.method_id("op7") == 7 and rt.method_id(11) == 11 and rt.method_id("3") == 3
+
+    def op9():
+        pass
+    assert rt.method_id(op9) == 9
+    for bad in (0, 12, "opx"):
+        with pytest.raises(ValueError):
+            rt.method_id(bad)
+
+
+def test_calibrated_tables():
+    assert rt.calibrated_step("1", 6)[0] == K.SIGMA / 2.55
+    assert rt.calibrated_step("2", 1) == (2 * np.pi / 4587, 4587)
+    assert rt.calibrated_step("4", 11)[0] == K.SIGMA / 2.74
+
+
+def test_sweep_candidates_sizes():
+    for uc, n in (("1", 200), ("2", 300), ("3", 200), ("4", 200)):
+        d, o, _ = api.sweep_candidates(uc)
+        assert len(d) == n == len(o)
+    d, o, dev = api.sweep_candidates("2")
+    assert d[0] == 303 and d[-1] == 4 and dev == 5
+
+
+def test_find_index_rules():
+    assert api.find_index_interface([0.1, 0.1, 0.3, 0.1], [0.5, 0.5, 0.9, 0.5], 0.2) == 1
+    assert api.find_index_interface([0.1, 0.1], [0.5, 0.5], 0.2) is None          # nothing above threshold
+    assert api.find_index_interface([0.1, 0.1, 0.3], [0.9, 0.5, 0.9], 0.2) is None  # max rule rejects every i
+    assert api.find_index_fisheye([1, 2, 6, 3], 5) == 1
+    assert api.find_index_fisheye([6, 1], 5) == -1                                  # reference quirk: i-1 = -1
+    assert api.find_index_fisheye([1, 2], 5) is None
+    assert api.find_index_vert([0.01, 0.02, 0.03, 0.06, 0.01], 0.05) == 2
+    assert api.find_index_vert([0.06, 0.01, 0.01], 0.05) is None
+
+
+def test_find_index_on_reference_metrics(golden_sweep):
+    """Selection rules applied to the reference's own sweep metrics give the reference's index."""
+    for key, uc in (("s2_op6", "2"), ("s2_op1", "2"), ("s3_op6", "3"), ("s3_op4", "3"), ("s4_op11", "4")):
+        metric = list(golden_sweep[key + "/metric"])
+        fn = api.find_index_fisheye if uc == "2" else api.find_index_vert
+        idx = fn(metric, 5 if uc == "2" else 0.05)
+        assert (-1 if idx is None else idx) == int(golden_sweep[key + "/index"])
+    idx = api.find_index_interface(list(golden_sweep["s1_op6/mean"]), list(golden_sweep["s1_op6/max"]), 0.2)
+    assert idx == int(golden_sweep["s1_op6/index"]) == 45   # divisor 2.55, the calibrated value RT:1424
+    assert round(api.sweep_candidates("1")[0][idx], 2) == 2.55
+
+
+def test_benchmark_statistic():
+    data = np.array([1.0, 1.1, 0.9, 1.0, 50.0, 1.05])
+    assert 50.0 not in api.remove_outliers_iqr(data)
+    seq = iter(np.tile([1.0, 1.01, 0.99, 1.0], 1000))
+    assert abs(api.benchmark_statistic(lambda: next(seq), trial=20) - 1.0) < 0.02
+
+
+def test_make_fan_sharding_consistent():
+    full = rt.make_fan("2", 1 << 12)
+    part = rt.make_fan("2", 1 << 12, 1000, 1100)
+    assert np.array_equal(full[0][1000:1100], part[0])
+    th = rt.make_fan("3", 1 << 10)[0]
+    assert th[0] == 0.0 and abs(th[-1] - np.pi / 2) < 1e-15
+
+
+def test_field_builder_matches_reference_bytes(golden_field):
+    """genZ + interpolacion restated in raytracing_b200.field produce the same spline the reference
+    evaluates (checked through the oracle's bit-exact field test) and the documented sizes."""
+    z, grd = rt.build_field("2")
+    assert z.tck[2].size == 261121 and len(grd[0].tck[0]) == 515
+    z, grd = rt.build_field("3")
+    assert grd[0].tck[2].size == 397243 and (len(grd[0].tck[0]), len(grd[0].tck[1])) == (543, 741)
