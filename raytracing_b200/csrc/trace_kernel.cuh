@@ -93,7 +93,9 @@ __global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
     int last_i = 0;
     int i = 1;
     const int Mloop = TRAJ ? a.max_size : M;
-    for (; i < Mloop; ++i) {
+    // The loop condition must be warp-uniform (lanes may have different M with per-ray max_sizes):
+    // every lane iterates until no lane of the warp is alive; `alive` drops at i+1 >= M.
+    for (;; ++i) {
         if (!__any_sync(0xffffffffu, alive)) break;
         if (alive) {
             double fx, fy, fang, fn, fgx, fgy;
