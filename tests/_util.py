@@ -25,7 +25,10 @@ def tolerances(sens, uc, m):
                 # step counts are integers and must be bit-exact unless the reference algorithm's own
                 # count moves under 1-ulp noise for that ray, or its positions wander by more than a
                 # step length's 1e-4 (then an exit test against the box can flip by one step)
-                unstable=set(s["unstable_rays"]), loose_steps=s["pos"] > 1e-7)
+                unstable=set(s["unstable_rays"]), loose_steps=s["pos"] > 1e-7,
+                # golden search on the interface far field (grad n == 0) is decided by libm's last bit and
+                # the near-critical rays amplify it chaotically: there a few rays may leave the band
+                chaotic=s["all"] > 1e-5)
 
 
 def close(a, b, tol):
@@ -61,3 +64,14 @@ def scenario_setup(uc):
     theta0, x0, y0 = rt.default_fan(uc)
     M = rt.max_size_for(uc, rt.DELTA_S, rt.DELTA_S_DIVISOR_FISHEYE + 1)
     return dict(z=z, grd=grd, gamma=c[0], box=c[5:9], theta0=theta0, x0=x0, y0=y0, M=M, step=rt.DELTA_S)
+
+
+def assert_close_rays(a, b, tol, what="", chaotic=False, max_outlier_frac=0.15):
+    """assert_close over arrays whose LAST axis is the ray index.  For combinations the sensitivity table
+    marks chaotic (interface op5/op9) up to max_outlier_frac of the rays may exceed the band."""
+    if not chaotic:
+        return assert_close(a, b, tol, what)
+    ok = close(a, b, tol)
+    per_ray = ok.reshape(-1, ok.shape[-1]).all(axis=0)
+    frac = 1.0 - per_ray.mean()
+    assert frac <= max_outlier_frac, "%s: %.0f%% of rays outside tol %.1e" % (what, 100 * frac, tol)

@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from _util import SCEN_METHODS, assert_close, check_steps, scenario_setup, tolerances
+from _util import SCEN_METHODS, assert_close, assert_close_rays, check_steps, scenario_setup, tolerances
 
 pytestmark = pytest.mark.gpu
 
@@ -45,16 +45,20 @@ def test_default_fan_vs_oracle_and_golden(engine, golden_traj, sensitivity, uc, 
     o = _oracle(s, uc, m)
     what = "s%s op%d" % (uc, m)
     same = check_steps(r.d_ray[2], o["d_ray"][2], tol, what)
-    assert_close(r.s_ray[:, :, same], o["s_ray"][:, :, same], tol["all"], what + " s_ray")
-    assert_close(r.d_ray[:2, same], o["d_ray"][:2, same], tol["d_ray"], what + " d_ray")
-    assert_close(r.last_row[:, same], o["final"][:, same], tol["all"], what + " last_row")
+    ch = tol["chaotic"]
+    assert_close_rays(r.s_ray[:, :, same], o["s_ray"][:, :, same], tol["all"], what + " s_ray", ch)
+    assert_close_rays(r.d_ray[:2, same], o["d_ray"][:2, same], tol["d_ray"], what + " d_ray", ch)
+    assert_close_rays(r.last_row[:, same], o["final"][:, same], tol["all"], what + " last_row", ch)
     if uc == "1":
-        assert_close(r.errors[same], o["errors"][same], tol["err"], what + " errors")
+        assert_close_rays(r.errors[same], o["errors"][same], tol["err"], what + " errors", ch)
+        # the physics metric the reference reports (RT:1395) agrees regardless
+        assert abs(np.mean(r.errors) - np.mean(o["errors"])) <= max(1e-9, 10 * tol["err"] / len(r.errors) ** 0.5)
     # golden rows straight from the reference
     key = "default_s%s_op%d/" % (uc, m)
     same_g = check_steps(r.d_ray[2], golden_traj[key + "d_ray"][2], tol, what + " golden")
     stride = int(golden_traj[key + "stride"])
-    assert_close(r.s_ray[::stride][:, :, same_g], golden_traj[key + "rows"][:, :, same_g], tol["all"], what + " golden rows")
+    assert_close_rays(r.s_ray[::stride][:, :, same_g], golden_traj[key + "rows"][:, :, same_g], tol["all"],
+                      what + " golden rows", ch)
     # rows after a ray's last step stay zero (np.zeros, RT:802)
     for k in range(0, r.s_ray.shape[2], 7):
         assert not r.s_ray[int(r.d_ray[2, k]) + 1:, :, k].any()
