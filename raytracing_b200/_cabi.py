@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librtb.so")
+LIB_PATH = os.environ.get("RTB_LIB_PATH") or os.path.join(_HERE, "csrc", "librtb.so")  # override: kernel tuning only
 
 RTB_PTR_HOST, RTB_PTR_DEVICE = 0, 1
 RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO = 1, 2, 4

@@ -1,0 +1,112 @@
+// fastmath.cuh -- branch-free FP64 building blocks for the default (non-faithful) kernels.
+//
+// ncu on the first faithful kernel (profiles/r1_*) showed 653 warp instructions per ray-step of
+// which only ~200 were FP64 arithmetic: libdevice sincos (range-reduction slow-path check, stack
+// frame), IEEE-754 division and sqrt sequences (slow-path branches) and their BSSY/BSYNC pairs made
+// the kernel issue-bound.  These replacements keep < 1 ulp-level accuracy (far inside the 1e-10
+// parity bar) with straight-line DFMA code so the FP64 pipe, not the issue slot, is the limiter.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace rtb {
+
+// 1/x for normal x (refractive indices, curvatures, anisotropy coefficients: all O(1e-8..1e3)).
+// MUFU.RCP64H seed (~20 bits) + two Newton steps -> < 1 ulp.
+__device__ __forceinline__ double rcp_fast(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+
+// 1/sqrt(x) for normal x > 0: MUFU.RSQ64H seed + two Newton steps.
+__device__ __forceinline__ double rsqrt_fast(double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x * y, y, 1.0);
+    y = fma(0.5 * y, e, y);
+    e = fma(-x * y, y, 1.0);
+    y = fma(0.5 * y, e, y);
+    return y;
+}
+
+// sqrt(x) for x >= 0 (0 -> 0), one residual correction on top of x * rsqrt(x).
+__device__ __forceinline__ double sqrt_fast(double x)
+{
+    const double xs = fmax(x, 1e-300);
+    const double y = rsqrt_fast(xs);
+    double s = xs * y;
+    const double r = fma(-s, s, xs);
+    s = fma(r, 0.5 * y, s);
+    return x > 0.0 ? s : 0.0;
+}
+
+// sin/cos kernels on |r| <= pi/4 (+ slack), minimax-quality Taylor coefficients in Horner form.
+__device__ __forceinline__ double sin_kernel(double r, double r2)
+{
+    double p = 1.58969099521155010221e-10;   //  1/13! region
+    p = fma(p, r2, -2.50507602534068634195e-08);
+    p = fma(p, r2, 2.75573137070700676789e-06);
+    p = fma(p, r2, -1.98412698298579493134e-04);
+    p = fma(p, r2, 8.33333333332248946124e-03);
+    p = fma(p, r2, -1.66666666666666324348e-01);
+    return fma(r * r2, p, r);
+}
+__device__ __forceinline__ double cos_kernel(double r2)
+{
+    double p = -1.13596475577881948265e-11;
+    p = fma(p, r2, 2.08757232129817482790e-09);
+    p = fma(p, r2, -2.75573143513906633035e-07);
+    p = fma(p, r2, 2.48015872894767294178e-05);
+    p = fma(p, r2, -1.38888888888741095749e-03);
+    p = fma(p, r2, 4.16666666666666019037e-02);
+    const double h = 0.5 * r2;
+    const double w = 1.0 - h;
+    return w + (((1.0 - w) - h) + r2 * r2 * p);
+}
+
+// sin and cos of a small increment |k| <= SMALL_ANGLE_MAX without range reduction.
+#define RTB_SMALL_ANGLE_MAX 0.7
+__device__ __forceinline__ void sincos_small(double k, double &s, double &c)
+{
+    const double k2 = k * k;
+    s = sin_kernel(k, k2);
+    c = cos_kernel(k2);
+}
+
+// (sin, cos)(theta + k) from (s0, c0) = (sin, cos)(theta) by the angle-addition formulas.
+__device__ __forceinline__ void rotate(double s0, double c0, double k, double &s, double &c)
+{
+    double sk, ck;
+    sincos_small(k, sk, ck);
+    s = fma(s0, ck, c0 * sk);
+    c = fma(c0, ck, -(s0 * sk));
+}
+
+static __device__ __noinline__ void sincos_libdevice(double x, double *s, double *c) { sincos(x, s, c); }
+
+// sin and cos for |x| up to ~1e5 (ray angles are O(1..100)): Cody-Waite reduction by pi/2 with a
+// 3-term split of pi/2, no slow path.  Larger arguments fall back to libdevice.
+__device__ __forceinline__ void sincos_cw(double x, double &s, double &c)
+{
+    if (fabs(x) > 1.0e5) { sincos_libdevice(x, &s, &c); return; }
+    const double q = rint(x * 6.36619772367581382433e-01); // x * 2/pi
+    double r = fma(q, -1.57079632673412561417e+00, x);      // pi/2 hi (33 bits)
+    r = fma(q, -6.07710050630396597660e-11, r);             // pi/2 mid
+    r = fma(q, -2.02226624879595063154e-21, r);             // pi/2 lo
+    const int n = __double2int_rn(q);
+    const double r2 = r * r;
+    const double sr = sin_kernel(r, r2);
+    const double cr = cos_kernel(r2);
+    double ss = (n & 1) ? cr : sr;
+    double cc = (n & 1) ? sr : cr;
+    s = (n & 2) ? -ss : ss;
+    c = ((n + 1) & 2) ? -cc : cc;
+}
+
+} // namespace rtb

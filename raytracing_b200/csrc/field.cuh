@@ -33,6 +33,11 @@ struct DevField {
     const double2 *cg; // interleaved {grd[0] = dn/dy, grd[1] = dn/dx}, (gu.n-4) x (gv.n-4)
     int ncz;           // row length of cz  = zv.n - zv.k - 1
     int ncg;           // row length of cg  = gv.n - gv.k - 1
+    // Fast path (host-verified in rtb_set_field): on [flo_u, fhi_u] x [flo_v, fhi_v] (cubic interval
+    // indices) all knots involved are uniform AND the bilinear knots coincide with the cubic ones
+    // shifted by one (tz[l-1] == tg[l]), so one interval / one fraction per physical axis serves all
+    // three splines.  fast_ok == 0 disables it (arbitrary user knots).
+    int fast_ok, flo_u, fhi_u, flo_v, fhi_v;
 };
 
 // FITPACK fpbisp interval search, restated for the GPU: clamp, then find l (0-based) with
@@ -145,6 +150,55 @@ __device__ __forceinline__ void n_gradient(const DevField &f, double x, double y
         gy = au; // grd[0] = d n / d y
         gx = av; // grd[1] = d n / d x
     }
+}
+
+// Rare general path of the default evaluator (near the grid ends / arbitrary knots): kept out of line
+// so its registers do not burden the step loop.
+static __device__ __noinline__ void n_gradient_general(const DevField &f, double x, double y, double *n, double *gx,
+                                                double *gy)
+{
+    n_gradient<false>(f, x, y, *n, *gx, *gy);
+}
+
+// Default evaluator: closed-form uniform basis, one interval computation per physical axis, no knot
+// comparisons (a fraction 1e-13 outside [0,1) evaluates the neighbouring polynomial piece of a C2 /
+// C0 spline: error << 1e-13).  Falls back to the general routine near the grid ends.
+__device__ __forceinline__ void n_gradient_fast(const DevField &f, double x, double y, double &n, double &gx,
+                                                double &gy)
+{
+    const int lu = __double2int_rd((y - f.gu_.t0) * f.gu_.inv_h) + f.gu_.off;
+    const int lv = __double2int_rd((x - f.gv_.t0) * f.gv_.inv_h) + f.gv_.off;
+    if (!f.fast_ok || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
+        n_gradient_general(f, x, y, &n, &gx, &gy);
+        return;
+    }
+    const double su = (y - __ldg(f.gu_.t + lu)) * f.gu_.inv_h;
+    const double sv = (x - __ldg(f.gv_.t + lv)) * f.gv_.inv_h;
+    {
+        const double *c = f.cz + (size_t)(lu - 2) * f.ncz + (lv - 2); // bilinear l = cubic l - 1
+        const double c00 = __ldg(c), c01 = __ldg(c + 1), c10 = __ldg(c + f.ncz), c11 = __ldg(c + f.ncz + 1);
+        const double r0 = fma(sv, c01 - c00, c00);
+        const double r1 = fma(sv, c11 - c10, c10);
+        n = fma(su, r1 - r0, r0);
+    }
+    double wu[4], wv[4];
+    basis_uniform3(su, wu);
+    basis_uniform3(sv, wv);
+    const double2 *c = f.cg + (size_t)(lu - 3) * f.ncg + (lv - 3);
+    double au = 0.0, av = 0.0;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const double2 c0 = __ldg(c), c1 = __ldg(c + 1), c2 = __ldg(c + 2), c3 = __ldg(c + 3);
+        double ru = c0.x * wv[0], rv = c0.y * wv[0];
+        ru = fma(c1.x, wv[1], ru); rv = fma(c1.y, wv[1], rv);
+        ru = fma(c2.x, wv[2], ru); rv = fma(c2.y, wv[2], rv);
+        ru = fma(c3.x, wv[3], ru); rv = fma(c3.y, wv[3], rv);
+        au = fma(ru, wu[a], au);
+        av = fma(rv, wu[a], av);
+        c += f.ncg;
+    }
+    gy = au;
+    gx = av;
 }
 
 } // namespace rtb

@@ -141,6 +141,7 @@ static int make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax)
     ax->tb = t[k]; ax->te = t[n - k - 1];
     ax->inv_h = 1.0 / h;
     if (bestB >= bestA) {
+        ax->inv_h = (double)(bestB + 1 - bestA) / (t[bestB + 1] - t[bestA]); // spacing over the whole run
         ax->t0 = t[bestA]; ax->off = bestA;
         ax->lo = bestA + k - 1; ax->hi = bestB - k + 1;
     } else {
@@ -180,6 +181,19 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
     CK(cudaMemcpy(dg, inter.data(), ng * sizeof(double2), cudaMemcpyHostToDevice));
     f.cz = dz;
     f.cg = dg;
+    // fast path: bilinear knots == cubic knots shifted by one over the uniform cubic range
+    auto shared_axis = [](const double *tz, int nz, const DevAxis &az, const double *tg, const DevAxis &ag, int &lo, int &hi) {
+        lo = ag.lo; hi = ag.hi;
+        if (hi < lo) return false;
+        if (lo - 1 < az.lo) lo = az.lo + 1;
+        if (hi - 1 > az.hi) hi = az.hi + 1;
+        if (hi < lo || hi + 1 >= nz + 1) return false;
+        for (int l = lo; l <= hi; ++l)
+            if (tz[l - 1] != tg[l] || tz[l] != tg[l + 1]) return false;
+        return true;
+    };
+    f.fast_ok = shared_axis(z->tu, z->nu, f.zu, gu->tu, f.gu_, f.flo_u, f.fhi_u) &&
+                shared_axis(z->tv, z->nv, f.zv, gu->tv, f.gv_, f.flo_v, f.fhi_v);
     ctx->f = f;
     ctx->has_field = true;
     return RTB_OK;

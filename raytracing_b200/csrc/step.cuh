@@ -18,6 +18,7 @@ struct RayState {
     double ux, uy;      // cos(ang), sin(ang)
     double n, gx, gy;   // field at (x,y)
     double coef;        // anisotropy(ang, gamma)
+    double inv_n;       // 1/n (default kernels only)
 };
 
 // Position advancer of each method: 1 = first_order_taylor, 2 = second_order_taylor, 3 = curvature_t

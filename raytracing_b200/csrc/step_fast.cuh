@@ -1,0 +1,200 @@
+// step_fast.cuh -- the eleven step methods (RT_bench.py:469-764) in the default B200 form:
+// same mathematics as step.cuh (the faithful restatement), re-associated for the FP64 pipe:
+//   * 1/n carried in the ray state (one Newton reciprocal per step instead of 4 IEEE divisions);
+//   * sin/cos of theta+k for the small increments of tfinal_2o / curvature_t by angle addition
+//     from the carried (sin, cos) with an exact resync every RESYNC steps;
+//   * theta_cost_t / finite_diff: the new unit vector is the normalised momentum / difference
+//     vector itself (cos(atan2(b,a)) = a/|(a,b)|), the atan2 is evaluated only where theta is
+//     stored (every kept row in trajectory mode, once at the end otherwise);
+//   * curvature_t without the reference's cancellation: sin(t+e)-sin(t) = s(cos e - 1) + c sin e.
+// Every deviation from the faithful kernel is rounding-level (<= 1e-13 over a trajectory, see
+// tests/test_gpu_trace.py) except where the reference itself is noise-dominated.
+#pragma once
+#include "fastmath.cuh"
+#include "step.cuh"
+
+namespace rtb {
+
+typedef RayState FastState; // ang is stale (lazy) for theta_cost_t / finite_diff methods when LAZY
+
+#define RTB_RESYNC_MASK 15 // exact sincos every 16 steps bounds the drift of the rotated (sin, cos)
+
+// cos(k) - 1 for |k| <= RTB_SMALL_ANGLE_MAX without cancellation
+__device__ __forceinline__ double cosm1_small(double k2)
+{
+    double p = -1.13596475577881948265e-11;
+    p = fma(p, k2, 2.08757232129817482790e-09);
+    p = fma(p, k2, -2.75573143513906633035e-07);
+    p = fma(p, k2, 2.48015872894767294178e-05);
+    p = fma(p, k2, -1.38888888888741095749e-03);
+    p = fma(p, k2, 4.16666666666666019037e-02);
+    return fma(k2 * k2, p, -0.5 * k2);
+}
+
+struct CostIsoFast {
+    double n1, ax, ay; // ax = n0*ux + impulse_x
+    __device__ __forceinline__ double operator()(double th) const
+    {
+        double s, c;
+        sincos_cw(th, s, c);
+        const double a = fma(n1, c, -ax), b = fma(n1, s, -ay);
+        return fma(a, a, b * b);
+    }
+};
+
+struct CostAnisoFast {
+    double n1, gamma, g2m1, mx, my, gx1h, gy1h; // mx = mi_x + h*coef_i*gx0/2 ; gx1h = h*gx1/2
+    __device__ __forceinline__ double operator()(double th) const
+    {
+        double s, c;
+        sincos_cw(th, s, c);
+        const double gs = gamma * s;
+        const double v = fma(gs, gs, c * c);
+        const double coef = sqrt_fast(v), iv = rcp_fast(v);
+        const double nc = n1 * coef, k = g2m1 * iv;
+        const double a = nc * c * fma(-(s * s), k, 1.0) - mx - coef * gx1h;
+        const double b = nc * s * fma(c * c, k, 1.0) - my - coef * gy1h;
+        return fma(a, a, b * b);
+    }
+};
+
+// One step.  Updates the state in place; returns dist = |r1 - r0|.  LAZY: theta of atan2-type
+// updaters is not evaluated (s.ang stale); `i` is the step index (resync schedule).
+template <int METHOD, bool ISO, bool LAZY>
+__device__ __forceinline__ double step_fast(const DevField &f, FastState &s, double h, double gamma, double g2m1,
+                                            double (&hist)[3][2], int i, bool bootstrap)
+{
+    constexpr int ADV = advancer_of(METHOD);
+    constexpr int UPD = updater_of(METHOD);
+    double fx, fy;
+    bool ignore = true;
+    const double dot = fma(s.gx, s.ux, s.gy * s.uy);
+    const double qx = fma(-dot, s.ux, s.gx), qy = fma(-dot, s.uy, s.gy); // grad n minus its tangential part
+    if (ADV == 1) {
+        fx = fma(s.ux, h, s.x);
+        fy = fma(s.uy, h, s.y);
+    } else if (ADV == 2 || bootstrap) {
+        const double q = 0.5 * h * h * s.inv_n;
+        fx = fma(qx, q, fma(s.ux, h, s.x));
+        fy = fma(qy, q, fma(s.uy, h, s.y));
+    } else {
+        const double q2 = fma(qx, qx, qy * qy);
+        const double curv = sqrt_fast(q2) * s.inv_n;
+        if (curv < RTB_GOLD_TOL) {
+            fx = fma(s.ux, h, s.x);
+            fy = fma(s.uy, h, s.y);
+            ignore = false;
+        } else {
+            const double d = curv * h;
+            const double sg = (s.gx * s.uy - s.gy * s.ux > 0) ? -1.0 : 1.0;
+            const double e = sg * d;
+            double ds, dc; // sin(t+e)-sin(t), cos(t+e)-cos(t)
+            if (d <= RTB_SMALL_ANGLE_MAX) {
+                const double e2 = e * e;
+                const double se = sin_kernel(e, e2), cm = cosm1_small(e2);
+                ds = fma(s.uy, cm, s.ux * se);
+                dc = fma(s.ux, cm, -(s.uy * se));
+            } else { // huge step * curvature: plain evaluation like the reference
+                const double ang = (s.ang != s.ang) ? atan2(s.uy, s.ux) : s.ang; // NaN = lazy theta
+                double s1, c1;
+                sincos_cw(ang + e, s1, c1);
+                ds = s1 - s.uy;
+                dc = c1 - s.ux;
+            }
+            const double icurv = s.n * rsqrt_fast(q2);
+            fx = fma(sg * ds, icurv, s.x);
+            fy = fma(-sg * dc, icurv, s.y);
+        }
+    }
+    double fn, fgx, fgy;
+    n_gradient_fast(f, fx, fy, fn, fgx, fgy);
+    const double inv_fn = rcp_fast(fn);
+
+    const double dx = s.x - fx, dy = s.y - fy;
+    const double dist = sqrt_fast(fma(dx, dx, dy * dy));
+
+    if (UPD == 3 || bootstrap) { // finite differences RT:370-372, bootstrap RT:843-857
+        double vx, vy;
+        if (bootstrap) {
+            if (i == 1) {
+                hist[1][0] = fx; hist[1][1] = fy;
+                vx = fx - hist[0][0]; vy = fy - hist[0][1];
+            } else {
+                hist[2][0] = fx; hist[2][1] = fy;
+                vx = 3 * fx - 4 * hist[1][0] + hist[0][0];
+                vy = 3 * fy - 4 * hist[1][1] + hist[0][1];
+            }
+        } else {
+            vx = 11 * fx - 18 * hist[2][0] + 9 * hist[1][0] - 2 * hist[0][0];
+            vy = 11 * fy - 18 * hist[2][1] + 9 * hist[1][1] - 2 * hist[0][1];
+            hist[0][0] = hist[1][0]; hist[0][1] = hist[1][1];
+            hist[1][0] = hist[2][0]; hist[1][1] = hist[2][1];
+            hist[2][0] = fx; hist[2][1] = fy;
+        }
+        const double r = rsqrt_fast(fma(vx, vx, vy * vy));
+        s.ux = vx * r; s.uy = vy * r;
+        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(vy, vx);
+    } else if (ADV == 3 && !ignore) {
+        // curvature below GOLD_TOL: angle and unit vector unchanged (op3/4/5/10)
+    } else if (UPD == 1) { // theta_cost_t RT:393-407
+        const double a = fma(0.5 * h, s.gx + fgx, s.n * s.ux);
+        const double b = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
+        const double r = rsqrt_fast(fma(a, a, b * b));
+        s.ux = a * r; s.uy = b * r;
+        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(b, a);
+    } else if (UPD == 2) { // tfinal_2o RT:374-391
+        const double k1 = h * (s.ux * s.gy - s.uy * s.gx) * s.inv_n;
+        double s1, c1;
+        if (fabs(k1) <= RTB_SMALL_ANGLE_MAX) rotate(s.uy, s.ux, k1, s1, c1);
+        else sincos_cw(s.ang + k1, s1, c1);
+        const double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
+        const double kf = 0.5 * (k1 + k2);
+        s.ang += kf;
+        if (fabs(kf) <= RTB_SMALL_ANGLE_MAX && (i & RTB_RESYNC_MASK) != 0) {
+            const double s0 = s.uy, c0 = s.ux;
+            rotate(s0, c0, kf, s.uy, s.ux);
+        } else {
+            sincos_cw(s.ang, s.uy, s.ux);
+        }
+    } else if (UPD == 4) { // golden, isotropic cost RT:595,697
+        CostIsoFast cf;
+        cf.n1 = fn;
+        cf.ax = fma(0.5 * h, s.gx + fgx, s.n * s.ux);
+        cf.ay = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
+        s.ang = golden(cf, s.ang - RTB_DELTA_G, s.ang + RTB_DELTA_G);
+        sincos_cw(s.ang, s.uy, s.ux);
+    } else { // golden, anisotropic cost RT:728,761
+        CostAnisoFast cf;
+        cf.n1 = fn; cf.gamma = gamma; cf.g2m1 = g2m1;
+        const double ic2 = rcp_fast(s.coef * s.coef);
+        const double nc = s.n * s.coef;
+        cf.mx = fma(0.5 * h * s.coef, s.gx, nc * s.ux * fma(-(s.uy * s.uy), g2m1 * ic2, 1.0));
+        cf.my = fma(0.5 * h * s.coef, s.gy, nc * s.uy * fma(s.ux * s.ux, g2m1 * ic2, 1.0));
+        cf.gx1h = 0.5 * h * fgx; cf.gy1h = 0.5 * h * fgy;
+        s.ang = golden(cf, s.ang - RTB_DELTA_G, s.ang + RTB_DELTA_G);
+        sincos_cw(s.ang, s.uy, s.ux);
+    }
+    s.x = fx; s.y = fy; s.n = fn; s.inv_n = inv_fn; s.gx = fgx; s.gy = fgy;
+    if (!ISO) {
+        const double gs = gamma * s.uy;
+        s.coef = sqrt_fast(fma(gs, gs, s.ux * s.ux));
+    }
+    return dist;
+}
+
+// moments RT:232-245 from the state
+template <bool ISO>
+__device__ __forceinline__ void moments_fast(const FastState &s, double g2m1, double &px, double &py)
+{
+    if (ISO) {
+        px = s.n * s.ux;
+        py = s.n * s.uy;
+    } else {
+        const double k = g2m1 * rcp_fast(s.coef * s.coef);
+        const double nc = s.n * s.coef;
+        px = nc * s.ux * fma(-(s.uy * s.uy), k, 1.0);
+        py = nc * s.uy * fma(s.ux * s.ux, k, 1.0);
+    }
+}
+
+} // namespace rtb

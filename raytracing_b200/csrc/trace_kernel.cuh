@@ -6,9 +6,13 @@
 // instruction, so trajectory write-back is coalesced by construction; streaming (.cs)
 // stores keep the 48 B/ray-step of output from evicting the spline tables out of L2.
 #pragma once
-#include "step.cuh"
+#include "step_fast.cuh"
 
 namespace rtb {
+
+#ifndef RTB_MIN_BLOCKS
+#define RTB_MIN_BLOCKS 5 // default kernels: <= 96 registers -> 5 blocks of 128 threads per SM
+#endif
 
 struct TraceArgs {
     DevField f;
@@ -42,9 +46,13 @@ __device__ __forceinline__ void store_row(double *p, int64_t R, double x, double
     __stcs(p + 5 * R, ang);
 }
 
+// EXACT = faithful restatement (reference evaluation order, libdevice sincos, IEEE div/sqrt, FITPACK
+// recurrence): the parity anchor.  !EXACT = default B200 form (step_fast.cuh).
 template <int METHOD, bool ISO, bool TRAJ, bool EXACT>
-__global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
+__global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(const TraceArgs a)
 {
+    constexpr int UPD = updater_of(METHOD);
+    constexpr bool LAZY = !EXACT && !TRAJ && (UPD == 1 || UPD == 3); // theta evaluated once at the end
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = r < a.R;
     const int64_t rr = valid ? r : a.R - 1; // padded lanes shadow the last ray, never store
@@ -63,8 +71,11 @@ __global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
     // INITIAL CONDITIONS RT:809-826
     RayState s;
     s.x = a.x0[rr]; s.y = a.y0[rr]; s.ang = a.theta0[rr];
-    sincos(s.ang, &s.uy, &s.ux);
-    n_gradient<EXACT>(a.f, s.x, s.y, s.n, s.gx, s.gy);
+    if (EXACT) sincos(s.ang, &s.uy, &s.ux);
+    else sincos_cw(s.ang, s.uy, s.ux);
+    if (EXACT) n_gradient<true>(a.f, s.x, s.y, s.n, s.gx, s.gy);
+    else n_gradient_fast(a.f, s.x, s.y, s.n, s.gx, s.gy);
+    s.inv_n = EXACT ? 0.0 : rcp_fast(s.n);
     s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
     double px, py;
     moments_sc<ISO>(s.n, s.coef, g2m1, s.ux, s.uy, px, py);
@@ -98,35 +109,41 @@ __global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
     for (;; ++i) {
         if (!__any_sync(0xffffffffu, alive)) break;
         if (alive) {
-            double fx, fy, fang, fn, fgx, fgy;
-            if (METHOD == 7 && i < 3) { // bootstrap RT:838-864
-                const double dot = s.gx * s.ux + s.gy * s.uy;
-                const double s2 = h * h, den = 2.0 * s.n;
-                fx = (s.x + s.ux * h) + (s.gx - dot * s.ux) * s2 / den;
-                fy = (s.y + s.uy * h) + (s.gy - dot * s.uy) * s2 / den;
-                n_gradient<EXACT>(a.f, fx, fy, fn, fgx, fgy);
-                double vx, vy; // static indices keep VECTOR_LIST in registers
-                if (i == 1) {
-                    hist[1][0] = fx; hist[1][1] = fy;
-                    vx = hist[1][0] - hist[0][0]; vy = hist[1][1] - hist[0][1];
+            double dist;
+            if (EXACT) {
+                double fx, fy, fang, fn, fgx, fgy;
+                if (METHOD == 7 && i < 3) { // bootstrap RT:838-864
+                    const double dot = s.gx * s.ux + s.gy * s.uy;
+                    const double s2 = h * h, den = 2.0 * s.n;
+                    fx = (s.x + s.ux * h) + (s.gx - dot * s.ux) * s2 / den;
+                    fy = (s.y + s.uy * h) + (s.gy - dot * s.uy) * s2 / den;
+                    n_gradient<true>(a.f, fx, fy, fn, fgx, fgy);
+                    double vx, vy; // static indices keep VECTOR_LIST in registers
+                    if (i == 1) {
+                        hist[1][0] = fx; hist[1][1] = fy;
+                        vx = hist[1][0] - hist[0][0]; vy = hist[1][1] - hist[0][1];
+                    } else {
+                        hist[2][0] = fx; hist[2][1] = fy;
+                        vx = 3 * hist[2][0] - 4 * hist[1][0] + hist[0][0];
+                        vy = 3 * hist[2][1] - 4 * hist[1][1] + hist[0][1];
+                    }
+                    fang = atan2(vy, vx);
                 } else {
-                    hist[2][0] = fx; hist[2][1] = fy;
-                    vx = 3 * hist[2][0] - 4 * hist[1][0] + hist[0][0];
-                    vy = 3 * hist[2][1] - 4 * hist[1][1] + hist[0][1];
+                    step_method<METHOD, true>(a.f, s, h, gamma, g2m1, hist, fx, fy, fang, fn, fgx, fgy);
                 }
-                fang = atan2(vy, vx);
+                // store_update_results RT:783-790
+                const double dx = s.x - fx, dy = s.y - fy;
+                dist = sqrt(dx * dx + dy * dy);
+                sincos(fang, &s.uy, &s.ux);
+                s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
+                moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
+                s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             } else {
-                step_method<METHOD, EXACT>(a.f, s, h, gamma, g2m1, hist, fx, fy, fang, fn, fgx, fgy);
+                dist = step_fast<METHOD, ISO, LAZY>(a.f, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3);
+                moments_fast<ISO>(s, g2m1, px, py);
             }
-            // store_update_results RT:783-790
-            const double dx = s.x - fx, dy = s.y - fy;
-            const double dist = sqrt(dx * dx + dy * dy);
             dist_sim += dist;
             dist_real += h;
-            sincos(fang, &s.uy, &s.ux);
-            s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
-            moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
-            s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             // RT:871-875
             const double nray = s.coef * s.n;
             T = T + dist * (nray_prev + nray) / 2.0;
@@ -168,13 +185,14 @@ __global__ void __launch_bounds__(128) trace_kernel(const TraceArgs a)
             }
         }
     }
+    if (LAZY && s.ang != s.ang) s.ang = atan2(s.uy, s.ux); // theta of the last row (NaN = not evaluated yet)
 
     // per-ray results RT:888-890
     if (valid) {
         if (a.d_ray) {
-        a.d_ray[r] = dist_real;
-        a.d_ray[a.R + r] = dist_sim;
-        a.d_ray[2 * a.R + r] = (double)last_i;
+            a.d_ray[r] = dist_real;
+            a.d_ray[a.R + r] = dist_sim;
+            a.d_ray[2 * a.R + r] = (double)last_i;
         }
         if (a.last_row) {
             a.last_row[r] = s.x; a.last_row[a.R + r] = s.y;
