@@ -46,25 +46,35 @@ __device__ __forceinline__ double sqrt_fast(double x)
     return x > 0.0 ? s : 0.0;
 }
 
+// Polynomial coefficients live in constant memory so DFMA reads them as c[bank][offset] operands
+// (as immediates each use costs two UMOV issue slots: 50 of 402 instructions per step in the first
+// default kernel, profiles/r1b_*).
+__constant__ double kSin[6] = {1.58969099521155010221e-10, -2.50507602534068634195e-08, 2.75573137070700676789e-06,
+                               -1.98412698298579493134e-04, 8.33333333332248946124e-03, -1.66666666666666324348e-01};
+__constant__ double kCos[6] = {-1.13596475577881948265e-11, 2.08757232129817482790e-09, -2.75573143513906633035e-07,
+                               2.48015872894767294178e-05, -1.38888888888741095749e-03, 4.16666666666666019037e-02};
+__constant__ double kPio2[4] = {6.36619772367581382433e-01, -1.57079632673412561417e+00, -6.07710050630396597660e-11,
+                                -2.02226624879595063154e-21};
+
 // sin/cos kernels on |r| <= pi/4 (+ slack), minimax-quality Taylor coefficients in Horner form.
 __device__ __forceinline__ double sin_kernel(double r, double r2)
 {
-    double p = 1.58969099521155010221e-10;   //  1/13! region
-    p = fma(p, r2, -2.50507602534068634195e-08);
-    p = fma(p, r2, 2.75573137070700676789e-06);
-    p = fma(p, r2, -1.98412698298579493134e-04);
-    p = fma(p, r2, 8.33333333332248946124e-03);
-    p = fma(p, r2, -1.66666666666666324348e-01);
+    double p = kSin[0];
+    p = fma(p, r2, kSin[1]);
+    p = fma(p, r2, kSin[2]);
+    p = fma(p, r2, kSin[3]);
+    p = fma(p, r2, kSin[4]);
+    p = fma(p, r2, kSin[5]);
     return fma(r * r2, p, r);
 }
 __device__ __forceinline__ double cos_kernel(double r2)
 {
-    double p = -1.13596475577881948265e-11;
-    p = fma(p, r2, 2.08757232129817482790e-09);
-    p = fma(p, r2, -2.75573143513906633035e-07);
-    p = fma(p, r2, 2.48015872894767294178e-05);
-    p = fma(p, r2, -1.38888888888741095749e-03);
-    p = fma(p, r2, 4.16666666666666019037e-02);
+    double p = kCos[0];
+    p = fma(p, r2, kCos[1]);
+    p = fma(p, r2, kCos[2]);
+    p = fma(p, r2, kCos[3]);
+    p = fma(p, r2, kCos[4]);
+    p = fma(p, r2, kCos[5]);
     const double h = 0.5 * r2;
     const double w = 1.0 - h;
     return w + (((1.0 - w) - h) + r2 * r2 * p);
@@ -88,17 +98,22 @@ __device__ __forceinline__ void rotate(double s0, double c0, double k, double &s
     c = fma(c0, ck, -(s0 * sk));
 }
 
-static __device__ __noinline__ void sincos_libdevice(double x, double *s, double *c) { sincos(x, s, c); }
+static __device__ __noinline__ double2 sincos_libdevice(double x)
+{
+    double2 r; // (sin, cos) by value: no address-taken locals in the caller
+    sincos(x, &r.x, &r.y);
+    return r;
+}
 
 // sin and cos for |x| up to ~1e5 (ray angles are O(1..100)): Cody-Waite reduction by pi/2 with a
 // 3-term split of pi/2, no slow path.  Larger arguments fall back to libdevice.
 __device__ __forceinline__ void sincos_cw(double x, double &s, double &c)
 {
-    if (fabs(x) > 1.0e5) { sincos_libdevice(x, &s, &c); return; }
-    const double q = rint(x * 6.36619772367581382433e-01); // x * 2/pi
-    double r = fma(q, -1.57079632673412561417e+00, x);      // pi/2 hi (33 bits)
-    r = fma(q, -6.07710050630396597660e-11, r);             // pi/2 mid
-    r = fma(q, -2.02226624879595063154e-21, r);             // pi/2 lo
+    if (fabs(x) > 1.0e5) { const double2 r = sincos_libdevice(x); s = r.x; c = r.y; return; }
+    const double q = rint(x * kPio2[0]); // x * 2/pi
+    double r = fma(q, kPio2[1], x);      // pi/2 hi (33 bits)
+    r = fma(q, kPio2[2], r);             // pi/2 mid
+    r = fma(q, kPio2[3], r);             // pi/2 lo
     const int n = __double2int_rn(q);
     const double r2 = r * r;
     const double sr = sin_kernel(r, r2);

@@ -154,22 +154,27 @@ __device__ __forceinline__ void n_gradient(const DevField &f, double x, double y
 
 // Rare general path of the default evaluator (near the grid ends / arbitrary knots): kept out of line
 // so its registers do not burden the step loop.
-static __device__ __noinline__ void n_gradient_general(const DevField &f, double x, double y, double *n, double *gx,
-                                                double *gy)
+// `fd` is the context's copy of the DevField in global memory (taking the address of the kernel
+// parameter would force a 700-byte local-memory copy of the whole parameter block).
+struct FieldSample { double n, gx, gy; };
+static __device__ __noinline__ FieldSample n_gradient_general(const DevField *fd, double x, double y)
 {
-    n_gradient<false>(f, x, y, *n, *gx, *gy);
+    FieldSample r; // returned by value: keeps the caller's n, gx, gy in registers
+    n_gradient<false>(*fd, x, y, r.n, r.gx, r.gy);
+    return r;
 }
 
 // Default evaluator: closed-form uniform basis, one interval computation per physical axis, no knot
 // comparisons (a fraction 1e-13 outside [0,1) evaluates the neighbouring polynomial piece of a C2 /
 // C0 spline: error << 1e-13).  Falls back to the general routine near the grid ends.
-__device__ __forceinline__ void n_gradient_fast(const DevField &f, double x, double y, double &n, double &gx,
-                                                double &gy)
+__device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevField *fd, double x, double y,
+                                                double &n, double &gx, double &gy)
 {
     const int lu = __double2int_rd((y - f.gu_.t0) * f.gu_.inv_h) + f.gu_.off;
     const int lv = __double2int_rd((x - f.gv_.t0) * f.gv_.inv_h) + f.gv_.off;
     if (!f.fast_ok || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
-        n_gradient_general(f, x, y, &n, &gx, &gy);
+        const FieldSample r = n_gradient_general(fd, x, y);
+        n = r.n; gx = r.gx; gy = r.gy;
         return;
     }
     const double su = (y - __ldg(f.gu_.t + lu)) * f.gu_.inv_h;

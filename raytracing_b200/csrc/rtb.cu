@@ -30,6 +30,7 @@ struct rtb_ctx {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool has_field = false;
     DevField f;
+    DevField *f_dev = nullptr;
     std::vector<void *> field_allocs;
     unsigned long long *d_total = nullptr;
     int block = 128;
@@ -195,6 +196,9 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
     f.fast_ok = shared_axis(z->tu, z->nu, f.zu, gu->tu, f.gu_, f.flo_u, f.fhi_u) &&
                 shared_axis(z->tv, z->nv, f.zv, gu->tv, f.gv_, f.flo_v, f.fhi_v);
     ctx->f = f;
+    CK(cudaMalloc(&ctx->f_dev, sizeof(DevField)));
+    ctx->field_allocs.push_back(ctx->f_dev);
+    CK(cudaMemcpy(ctx->f_dev, &f, sizeof(DevField), cudaMemcpyHostToDevice));
     ctx->has_field = true;
     return RTB_OK;
 }
@@ -249,13 +253,14 @@ struct Staging {
 };
 
 template <bool EXACT>
-__global__ void field_eval_kernel(DevField f, const double *x, const double *y, int64_t n, double *on,
+__global__ void field_eval_kernel(DevField f, const DevField *fd, const double *x, const double *y, int64_t n, double *on,
                                   double *ogx, double *ogy)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double vn, gx, gy;
-    n_gradient<EXACT>(f, x[i], y[i], vn, gx, gy);
+    if (EXACT) n_gradient<true>(f, x[i], y[i], vn, gx, gy);
+    else n_gradient_fast(f, fd, x[i], y[i], vn, gx, gy);
     on[i] = vn; ogx[i] = gx; ogy[i] = gy;
 }
 
@@ -272,8 +277,8 @@ extern "C" int rtb_field_eval(rtb_ctx *ctx, int32_t ptr_kind, uint32_t flags, co
     double *dn = st.out(out_n, n), *dgx = st.out(out_gx, n), *dgy = st.out(out_gy, n);
     if (st.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_field_eval: staging", st.err);
     const unsigned grid = (unsigned)((n + 127) / 128);
-    if (flags & RTB_F_EXACT_BASIS) field_eval_kernel<true><<<grid, 128, 0, ctx->stream>>>(ctx->f, dx, dy, n, dn, dgx, dgy);
-    else field_eval_kernel<false><<<grid, 128, 0, ctx->stream>>>(ctx->f, dx, dy, n, dn, dgx, dgy);
+    if (flags & RTB_F_EXACT_BASIS) field_eval_kernel<true><<<grid, 128, 0, ctx->stream>>>(ctx->f, ctx->f_dev, dx, dy, n, dn, dgx, dgy);
+    else field_eval_kernel<false><<<grid, 128, 0, ctx->stream>>>(ctx->f, ctx->f_dev, dx, dy, n, dn, dgx, dgy);
     CK(cudaGetLastError());
     st.copy_back();
     CK(cudaStreamSynchronize(ctx->stream));
@@ -357,6 +362,7 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     TraceArgs a;
     std::memset(&a, 0, sizeof(a));
     a.f = ctx->f;
+    a.f_dev = ctx->f_dev;
     a.theta0 = sg.in(theta0, R); a.x0 = sg.in(x0, R); a.y0 = sg.in(y0, R);
     a.steps = sg.in(p->steps, R); a.max_sizes = sg.in(p->max_sizes, R);
     a.R = R; a.max_size = (int)p->max_size; a.out_stride = stride;

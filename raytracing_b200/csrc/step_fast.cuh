@@ -22,12 +22,12 @@ typedef RayState FastState; // ang is stale (lazy) for theta_cost_t / finite_dif
 // cos(k) - 1 for |k| <= RTB_SMALL_ANGLE_MAX without cancellation
 __device__ __forceinline__ double cosm1_small(double k2)
 {
-    double p = -1.13596475577881948265e-11;
-    p = fma(p, k2, 2.08757232129817482790e-09);
-    p = fma(p, k2, -2.75573143513906633035e-07);
-    p = fma(p, k2, 2.48015872894767294178e-05);
-    p = fma(p, k2, -1.38888888888741095749e-03);
-    p = fma(p, k2, 4.16666666666666019037e-02);
+    double p = kCos[0];
+    p = fma(p, k2, kCos[1]);
+    p = fma(p, k2, kCos[2]);
+    p = fma(p, k2, kCos[3]);
+    p = fma(p, k2, kCos[4]);
+    p = fma(p, k2, kCos[5]);
     return fma(k2 * k2, p, -0.5 * k2);
 }
 
@@ -61,7 +61,7 @@ struct CostAnisoFast {
 // One step.  Updates the state in place; returns dist = |r1 - r0|.  LAZY: theta of atan2-type
 // updaters is not evaluated (s.ang stale); `i` is the step index (resync schedule).
 template <int METHOD, bool ISO, bool LAZY>
-__device__ __forceinline__ double step_fast(const DevField &f, FastState &s, double h, double gamma, double g2m1,
+__device__ __forceinline__ double step_fast(const DevField &f, const DevField *fd, FastState &s, double h, double gamma, double g2m1,
                                             double (&hist)[3][2], int i, bool bootstrap)
 {
     constexpr int ADV = advancer_of(METHOD);
@@ -107,7 +107,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, FastState &s, dou
         }
     }
     double fn, fgx, fgy;
-    n_gradient_fast(f, fx, fy, fn, fgx, fgy);
+    n_gradient_fast(f, fd, fx, fy, fn, fgx, fgy);
     const double inv_fn = rcp_fast(fn);
 
     const double dx = s.x - fx, dy = s.y - fy;
@@ -133,7 +133,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, FastState &s, dou
         }
         const double r = rsqrt_fast(fma(vx, vx, vy * vy));
         s.ux = vx * r; s.uy = vy * r;
-        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(vy, vx);
+        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux); // same value in every output mode
     } else if (ADV == 3 && !ignore) {
         // curvature below GOLD_TOL: angle and unit vector unchanged (op3/4/5/10)
     } else if (UPD == 1) { // theta_cost_t RT:393-407
@@ -141,7 +141,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, FastState &s, dou
         const double b = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
         const double r = rsqrt_fast(fma(a, a, b * b));
         s.ux = a * r; s.uy = b * r;
-        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(b, a);
+        s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux);
     } else if (UPD == 2) { // tfinal_2o RT:374-391
         const double k1 = h * (s.ux * s.gy - s.uy * s.gx) * s.inv_n;
         double s1, c1;

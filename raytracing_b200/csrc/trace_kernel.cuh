@@ -16,6 +16,7 @@ namespace rtb {
 
 struct TraceArgs {
     DevField f;
+    const DevField *f_dev;     // the same struct in global memory (rare out-of-line paths)
     const double *theta0, *x0, *y0;
     const double *steps;       // per-ray step or nullptr
     const int64_t *max_sizes;  // per-ray max_size or nullptr
@@ -48,7 +49,9 @@ __device__ __forceinline__ void store_row(double *p, int64_t R, double x, double
 
 // EXACT = faithful restatement (reference evaluation order, libdevice sincos, IEEE div/sqrt, FITPACK
 // recurrence): the parity anchor.  !EXACT = default B200 form (step_fast.cuh).
-template <int METHOD, bool ISO, bool TRAJ, bool EXACT>
+// EXTRA = p_x statistics and/or Snell row capture requested (kept out of the plain kernels: their
+// accumulators cost 15 registers).
+template <int METHOD, bool ISO, bool TRAJ, bool EXACT, bool EXTRA>
 __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(const TraceArgs a)
 {
     constexpr int UPD = updater_of(METHOD);
@@ -62,7 +65,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
     const double g2m1 = gamma * gamma - 1.0;
 
     int cap_a = -1, cap_b = -1;
-    if (!TRAJ && a.cap_rows) {
+    if (EXTRA && !TRAJ && a.cap_rows) {
         cap_a = a.cap_rows[rr];
         cap_b = a.cap_rows[a.R + rr];
         M = min(M, cap_b + 1); // pass 2 stops at the later captured row
@@ -74,7 +77,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
     if (EXACT) sincos(s.ang, &s.uy, &s.ux);
     else sincos_cw(s.ang, s.uy, s.ux);
     if (EXACT) n_gradient<true>(a.f, s.x, s.y, s.n, s.gx, s.gy);
-    else n_gradient_fast(a.f, s.x, s.y, s.n, s.gx, s.gy);
+    else n_gradient_fast(a.f, a.f_dev, s.x, s.y, s.n, s.gx, s.gy);
     s.inv_n = EXACT ? 0.0 : rcp_fast(s.n);
     s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
     double px, py;
@@ -85,11 +88,11 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
     // p_x statistics over the non-zero entries (np.ma.masked_equal(...,0), RT:1358): shifted sums
     double st_shift = 0.0, st_s1 = 0.0, st_s2 = 0.0;
     int st_cnt = 0;
-    if (px != 0.0) { st_shift = px; st_cnt = 1; }
+    if (EXTRA && px != 0.0) { st_shift = px; st_cnt = 1; }
 
     double capv[4] = {0, 0, 0, 0};
-    if (cap_a == 0) { capv[0] = s.x; capv[1] = s.y; }
-    if (cap_b == 0) { capv[2] = s.x; capv[3] = s.y; }
+    if (EXTRA && cap_a == 0) { capv[0] = s.x; capv[1] = s.y; }
+    if (EXTRA && cap_b == 0) { capv[2] = s.x; capv[3] = s.y; }
 
     double *sp = nullptr;
     int next_keep = 0; // next row index that is kept in s_ray
@@ -139,7 +142,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
                 s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             } else {
-                dist = step_fast<METHOD, ISO, LAZY>(a.f, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3);
+                dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3);
                 moments_fast<ISO>(s, g2m1, px, py);
             }
             dist_sim += dist;
@@ -149,14 +152,14 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
             T = T + dist * (nray_prev + nray) / 2.0;
             nray_prev = nray;
             last_i = i;
-            if (px != 0.0) {
+            if (EXTRA && px != 0.0) {
                 if (st_cnt == 0) st_shift = px;
                 const double d = px - st_shift;
                 st_s1 += d;
                 st_s2 = fma(d, d, st_s2);
                 ++st_cnt;
             }
-            if (!TRAJ) {
+            if (EXTRA && !TRAJ) {
                 if (i == cap_a) { capv[0] = s.x; capv[1] = s.y; }
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
             }
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
             a.last_row[2 * a.R + r] = px; a.last_row[3 * a.R + r] = py;
             a.last_row[4 * a.R + r] = T; a.last_row[5 * a.R + r] = s.ang;
         }
-        if (a.px_stats) {
+        if (EXTRA && a.px_stats) {
             double mean = 0.0, sd = 0.0;
             if (st_cnt > 0) {
                 const double m1 = st_s1 / st_cnt;
@@ -211,7 +214,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
             a.px_stats[a.R + r] = mean;
             a.px_stats[2 * a.R + r] = sd;
         }
-        if (!TRAJ && a.cap_out) {
+        if (EXTRA && !TRAJ && a.cap_out) {
             a.cap_out[r] = capv[0]; a.cap_out[a.R + r] = capv[1];
             a.cap_out[2 * a.R + r] = capv[2]; a.cap_out[3 * a.R + r] = capv[3];
         }
@@ -231,7 +234,12 @@ template <int METHOD>
 cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
 {
     const unsigned grid = (unsigned)((a.R + block - 1) / block);
-#define RTB_L(I, T, E) trace_kernel<METHOD, I, T, E><<<grid, block, 0, st>>>(a)
+    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr;
+#define RTB_L(I, T, E)                                                                  \
+    do {                                                                                \
+        if (extra) trace_kernel<METHOD, I, T, E, true><<<grid, block, 0, st>>>(a);      \
+        else trace_kernel<METHOD, I, T, E, false><<<grid, block, 0, st>>>(a);           \
+    } while (0)
     if (iso) {
         if (traj) { if (exact) RTB_L(true, true, true); else RTB_L(true, true, false); }
         else      { if (exact) RTB_L(true, false, true); else RTB_L(true, false, false); }
