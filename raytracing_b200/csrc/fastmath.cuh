@@ -89,13 +89,44 @@ __device__ __forceinline__ void sincos_small(double k, double &s, double &c)
     c = cos_kernel(k2);
 }
 
-// (sin, cos)(theta + k) from (s0, c0) = (sin, cos)(theta) by the angle-addition formulas.
+// sqrt(x) for x > 0 strictly (step lengths): one Newton step on the rsqrt seed (40 bits) and one
+// residual correction of the product (-> < 1 ulp).
+__device__ __forceinline__ double sqrt_pos(double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double e = fma(-x * y, y, 1.0);
+    y = fma(0.5 * y, e, y);
+    double s = x * y;
+    const double r = fma(-s, s, x);
+    return fma(r, 0.5 * y, s);
+}
+
+// (sin, cos)(theta + k) from (s0, c0) = (sin, cos)(theta) by the angle-addition formulas, written as
+// a correction to (s0, c0): s = s0 + (s0 (cos k - 1) + c0 sin k).  The polynomial degree adapts to
+// |k| (per-step angle increments are 1e-5..1e-2; all tiers are accurate to < 1e-17 absolute).
 __device__ __forceinline__ void rotate(double s0, double c0, double k, double &s, double &c)
 {
-    double sk, ck;
-    sincos_small(k, sk, ck);
-    s = fma(s0, ck, c0 * sk);
-    c = fma(c0, ck, -(s0 * sk));
+    const double k2 = k * k;
+    double sk, cm; // sin k, cos k - 1
+    if (k2 < 1.0e-6) {
+        sk = fma(k * k2, -1.0 / 6.0, k);
+        cm = k2 * fma(k2, 1.0 / 24.0, -0.5);
+    } else if (k2 < 4.0e-4) {
+        sk = fma(k * k2, fma(k2, fma(k2, -1.0 / 5040.0, 1.0 / 120.0), -1.0 / 6.0), k);
+        cm = k2 * fma(k2, fma(k2, -1.0 / 720.0, 1.0 / 24.0), -0.5);
+    } else {
+        sk = sin_kernel(k, k2);
+        double p = kCos[0];
+        p = fma(p, k2, kCos[1]);
+        p = fma(p, k2, kCos[2]);
+        p = fma(p, k2, kCos[3]);
+        p = fma(p, k2, kCos[4]);
+        p = fma(p, k2, kCos[5]);
+        cm = fma(k2 * k2, p, -0.5 * k2);
+    }
+    s = s0 + fma(s0, cm, c0 * sk);
+    c = c0 + fma(c0, cm, -(s0 * sk));
 }
 
 static __device__ __noinline__ double2 sincos_libdevice(double x)

@@ -111,7 +111,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
     const double inv_fn = rcp_fast(fn);
 
     const double dx = s.x - fx, dy = s.y - fy;
-    const double dist = sqrt_fast(fma(dx, dx, dy * dy));
+    const double dist = sqrt_pos(fma(dx, dx, dy * dy));
 
     if (UPD == 3 || bootstrap) { // finite differences RT:370-372, bootstrap RT:843-857
         double vx, vy;
@@ -150,9 +150,9 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         const double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
         const double kf = 0.5 * (k1 + k2);
         s.ang += kf;
-        if (fabs(kf) <= RTB_SMALL_ANGLE_MAX && (i & RTB_RESYNC_MASK) != 0) {
-            const double s0 = s.uy, c0 = s.ux;
-            rotate(s0, c0, kf, s.uy, s.ux);
+        // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
+        if (fabs(k1) <= RTB_SMALL_ANGLE_MAX && fabs(kf) <= RTB_SMALL_ANGLE_MAX && (i & RTB_RESYNC_MASK) != 0) {
+            rotate(s1, c1, 0.5 * (k2 - k1), s.uy, s.ux);
         } else {
             sincos_cw(s.ang, s.uy, s.ux);
         }
