@@ -69,6 +69,15 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def host_cores():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which the oracle's
+    explicit omp_set_num_threads overrides)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_port_rate(sample_rays, nthreads):
     """Time the oracle (C port of the reference algorithm) on a bounded slice of the same fan."""
     import raytracing_b200 as rt
@@ -94,8 +103,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import rt_oracle as O
-    cores = O.max_threads()
+    cores = host_cores()
     sample = 4096
     for _ in range(args.warmup):
         cpu_port_rate(256, cores)
@@ -255,8 +263,7 @@ def run_cuda(args):
                               "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"})
             line["full_trajectory_mode"] = full_info
         if world == 1 and not args.no_cpu:
-            from oracle import rt_oracle as O
-            cores = O.max_threads()
+            cores = host_cores()
             s, dt = cpu_port_rate(4096, cores)
             line["cpu_baseline"] = {"value": s / dt, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "4096-ray strided slice of the same fan (%d ray-steps), oracle C port, "

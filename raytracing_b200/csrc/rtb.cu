@@ -35,6 +35,9 @@ struct rtb_ctx {
     unsigned long long *d_total = nullptr;
     int block = 128;
     std::string err;
+    // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
+    struct PoolBuf { void *p; size_t bytes; bool used; };
+    std::vector<PoolBuf> pool;
 };
 
 static int fail(rtb_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess)
@@ -91,6 +94,7 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     free_field(ctx);
+    for (auto &b : ctx->pool) cudaFree(b.p);
     if (ctx->d_total) cudaFree(ctx->d_total);
     for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -215,12 +219,31 @@ struct Staging {
     int64_t h2d = 0, d2h = 0;
     cudaError_t err = cudaSuccess;
     Staging(rtb_ctx *c, bool h) : ctx(c), host(h) {}
-    ~Staging() { for (void *p : tmp) cudaFree(p); }
+    ~Staging()
+    {
+        for (void *p : tmp)
+            for (auto &b : ctx->pool) if (b.p == p) b.used = false;
+    }
     void *alloc(size_t bytes)
     {
+        if (!bytes) bytes = 8;
+        rtb_ctx::PoolBuf *best = nullptr;
+        for (auto &b : ctx->pool)
+            if (!b.used && b.bytes >= bytes && (!best || b.bytes < best->bytes)) best = &b;
+        if (best && best->bytes <= 2 * bytes + (1 << 20)) {
+            best->used = true;
+            tmp.push_back(best->p);
+            return best->p;
+        }
         void *d = nullptr;
-        cudaError_t e = cudaMalloc(&d, bytes ? bytes : 8);
+        cudaError_t e = cudaMalloc(&d, bytes);
+        if (e != cudaSuccess) { // release idle pool memory and retry once
+            for (auto it = ctx->pool.begin(); it != ctx->pool.end();)
+                if (!it->used) { cudaFree(it->p); it = ctx->pool.erase(it); } else ++it;
+            e = cudaMalloc(&d, bytes);
+        }
         if (e != cudaSuccess) { err = e; return nullptr; }
+        ctx->pool.push_back({d, bytes, true});
         tmp.push_back(d);
         return d;
     }
