@@ -46,7 +46,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -190,6 +190,10 @@ def run_cuda(args):
     if world > 1:
         dist.barrier()
     t_ms = sum(a.elapsed_time(b) for a, b in ev)
+    # the event pairs must bracket the kernels (same stream): a step cannot be shorter than its kernel
+    if t_ms < 0.99 * sum(kernel_ms):
+        raise RuntimeError("timing events (%.3f ms) do not bracket the kernels (%.3f ms): stream mismatch"
+                           % (t_ms, sum(kernel_ms)))
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end through the public host-buffer API: pinned host inputs, H2D + D2H inside the call

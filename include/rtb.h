@@ -94,7 +94,8 @@ typedef struct {
 /* Create / destroy the per-GPU context (replaces the reference's process-global state). */
 int rtb_create(int device, rtb_ctx **out);
 void rtb_destroy(rtb_ctx *ctx);
-/* Launch on an existing stream (e.g. torch.cuda.current_stream().cuda_stream); NULL = own stream. */
+/* Launch on an existing stream (e.g. torch.cuda.current_stream().cuda_stream); NULL = own stream.
+   The legacy default stream must be named explicitly as cudaStreamLegacy ((void*)0x1). */
 int rtb_set_stream(rtb_ctx *ctx, void *cuda_stream);
 const char *rtb_last_error(rtb_ctx *ctx);
 int rtb_abi_version(void);

@@ -91,7 +91,10 @@ class Engine:
     def use_torch_stream(self):
         """Launch on torch's current stream so torch.cuda.Event timing brackets the kernels."""
         import torch
-        self._check(self._lib.rtb_set_stream(self._ctx, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        h = torch.cuda.current_stream(self.device).cuda_stream
+        # torch's default stream has handle 0, which rtb_set_stream reads as "own stream": pass the
+        # explicit legacy-default-stream handle (cudaStreamLegacy == 0x1) instead
+        self._check(self._lib.rtb_set_stream(self._ctx, C.c_void_p(h if h else 1)))
 
     def set_field(self, z, grd):
         """Upload z (bilinear n) and grd = (dn/dy spline, dn/dx spline) as interpolacion() returns
