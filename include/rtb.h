@@ -129,6 +129,55 @@ int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const dou
               double *last_row, double *px_stats, rtb_stats *stats);
 
 /*
+ * Batched two-point shooting search (BASELINE.json configs[4]).  The reference has NO two-point
+ * search -- README.md:6 "shooting method" is the forward fan of trazar, and scipy.optimize.minimize
+ * is imported (RT:48) but never called -- so these two calls are defined from reference parts
+ * (trazar RT:766-948 for every ray, golden RT:175-199 for the launch-angle refinement) and are
+ * parity-unpinned; DESIGN.md section 7 gives the definition, oracle/shoot_oracle.py the CPU restatement.
+ *
+ * All rays start at (src_x, src_y).  C DELTA_S candidates (steps[c], max_sizes[c]) are searched at
+ * once (the sweep of RT:1303-1318 as a batch axis).  p->method/flags/ptr_kind/gamma/box are used as in
+ * rtb_trace; p->step, p->max_size, p->steps, p->max_sizes are ignored.
+ * "Exit point" of a ray: where its last segment crosses the box (linear interpolation between the
+ * last row inside and the first row outside, RT:878), travel time (s_ray column 4) interpolated alike;
+ * a ray that never leaves reports its last row.
+ */
+typedef struct {
+    double src_x, src_y;
+    const double *steps;       /* (C) DELTA_S candidates                                    */
+    const int64_t *max_sizes;  /* (C) rows per candidate, ceil(s/step)+1 (RT:799)           */
+    int64_t C;
+    const double *target_x;    /* (Tn) target points                                        */
+    const double *target_y;
+    int64_t Tn;
+} rtb_shoot_problem;
+
+/*
+ * Coarse phase: integrate the fan angles[0..A) for every candidate (C*A rays, one launch) and, for
+ * each (candidate, target), find the first angle whose exit point is closest to the target.
+ *   exit_xyT (3, C, A) or NULL : exit x, y and travel time of every coarse ray
+ *   miss2    (C, Tn)           : smallest squared miss distance
+ *   index    (C, Tn)           : index0 + argmin_j  (index0 = global index of angles[0] when the fan is
+ *                                sharded by angle over several GPUs; reduce (miss2, index) with MIN)
+ */
+int rtb_shoot_coarse(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const double *angles,
+                     int64_t A, int64_t index0, double *exit_xyT, double *miss2, int64_t *index,
+                     rtb_stats *stats);
+
+/*
+ * Refinement: golden(f, lo, hi) of RT:175-199 for every (candidate, target) pair, with
+ * f(theta) = squared miss distance of the ray launched at theta; every iteration re-traces both
+ * probes of all pairs in one launch (2*C*Tn rays); pairs whose |c-d| <= GOLD_TOL stop tracing.
+ *   lo, hi   (C, Tn) : brackets (e.g. the coarse neighbours angles[j-1], angles[j+1])
+ *   theta    (C, Tn) : (a+b)/2 after convergence
+ *   result   (5, C, Tn): miss distance, travel time, exit x, exit y, steps taken, of the ray at theta
+ *   iterations        : golden iterations executed (max over pairs)
+ */
+int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const double *lo,
+                     const double *hi, double *theta, double *result, int64_t *iterations,
+                     rtb_stats *stats);
+
+/*
  * Measured FP64 pipe peak (dependent-free DFMA streams on every SM), the roofline denominator
  * of SURVEY.md 8(d); returns FLOP/s (2 per DFMA).
  */

@@ -11,5 +11,7 @@ from .fans import make_fan
 from .api import (trazar, search_delta, n_gradient, find_delta_s, sweep_candidates, sweep_metrics,
                   find_index_interface, find_index_fisheye, find_index_vert, px_cv,
                   remove_outliers_iqr, benchmark_statistic, get_engine)
+from .shooting import (shooting_search, targets_from_angles, sweep_two_point, brackets_from_index,
+                       reduce_argmin, candidate_rows, default_source)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -12,7 +12,7 @@ RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -
 
 # every symbol include/rtb.h declares
 EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
-           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak")
+           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine")
 
 
 class RtbSpline(C.Structure):
@@ -30,6 +30,11 @@ class RtbParams(C.Structure):
 class RtbStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double), ("ray_steps", C.c_int64),
                 ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64)]
+
+
+class RtbShootProblem(C.Structure):
+    _fields_ = [("src_x", C.c_double), ("src_y", C.c_double), ("steps", C.c_void_p), ("max_sizes", C.c_void_p),
+                ("C", C.c_int64), ("target_x", C.c_void_p), ("target_y", C.c_void_p), ("Tn", C.c_int64)]
 
 
 class RtbError(RuntimeError):
@@ -69,5 +74,11 @@ def load():
     lib.rtb_trace.argtypes = [vp, C.POINTER(RtbParams), vp, vp, vp, i64, vp, vp, vp, vp, vp, C.POINTER(RtbStats)]
     lib.rtb_fp64_peak.restype = C.c_int
     lib.rtb_fp64_peak.argtypes = [vp, C.POINTER(C.c_double)]
+    lib.rtb_shoot_coarse.restype = C.c_int
+    lib.rtb_shoot_coarse.argtypes = [vp, C.POINTER(RtbParams), C.POINTER(RtbShootProblem), vp, i64, i64, vp, vp, vp,
+                                     C.POINTER(RtbStats)]
+    lib.rtb_shoot_refine.restype = C.c_int
+    lib.rtb_shoot_refine.argtypes = [vp, C.POINTER(RtbParams), C.POINTER(RtbShootProblem), vp, vp, vp, vp,
+                                     C.POINTER(i64), C.POINTER(RtbStats)]
     _lib = lib
     return lib

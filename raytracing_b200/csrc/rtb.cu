@@ -1,58 +1,7 @@
 // rtb.cu -- C ABI (include/rtb.h) of the B200 ray-stepping engine: context, field upload,
 // staging, kernel dispatch, Snell metric, FP64 peak probe.  No CPU fallback anywhere: every
 // entry point needs a CUDA device and reports failures through the return code.
-#include "../../include/rtb.h"
-#include "trace_kernel.cuh"
-
-#include <algorithm>
-#include <cmath>
-#include <cstdio>
-#include <cstring>
-#include <string>
-#include <vector>
-
-namespace rtb {
-#define RTB_DECL(K) cudaError_t launch_trace_m##K(const TraceArgs &, bool, bool, bool, int, cudaStream_t);
-RTB_DECL(1) RTB_DECL(2) RTB_DECL(3) RTB_DECL(4) RTB_DECL(5) RTB_DECL(6)
-RTB_DECL(7) RTB_DECL(8) RTB_DECL(9) RTB_DECL(10) RTB_DECL(11)
-#undef RTB_DECL
-static const launch_fn kLaunch[12] = {nullptr, launch_trace_m1, launch_trace_m2, launch_trace_m3,
-                                      launch_trace_m4, launch_trace_m5, launch_trace_m6, launch_trace_m7,
-                                      launch_trace_m8, launch_trace_m9, launch_trace_m10, launch_trace_m11};
-} // namespace rtb
-
-using namespace rtb;
-
-struct rtb_ctx {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool own_stream = false;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    bool has_field = false;
-    DevField f;
-    DevField *f_dev = nullptr;
-    std::vector<void *> field_allocs;
-    unsigned long long *d_total = nullptr;
-    int block = 128;
-    std::string err;
-    // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
-    struct PoolBuf { void *p; size_t bytes; bool used; };
-    std::vector<PoolBuf> pool;
-};
-
-static int fail(rtb_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess)
-{
-    if (c) {
-        c->err = what;
-        if (e != cudaSuccess) { c->err += ": "; c->err += cudaGetErrorString(e); }
-    }
-    return code;
-}
-#define CK(call)                                                              \
-    do {                                                                      \
-        cudaError_t e_ = (call);                                              \
-        if (e_ != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, #call, e_);     \
-    } while (0)
+#include "ctx.cuh"
 
 extern "C" int rtb_abi_version(void) { return RTB_ABI_VERSION; }
 
@@ -206,74 +155,6 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
     ctx->has_field = true;
     return RTB_OK;
 }
-
-// ---------------------------------------------------------------------------------------
-// Staging: with RTB_PTR_HOST the library owns temporary device buffers for the call.
-// ---------------------------------------------------------------------------------------
-struct Staging {
-    rtb_ctx *ctx;
-    bool host;
-    std::vector<void *> tmp;
-    struct Back { void *host; void *dev; size_t bytes; };
-    std::vector<Back> back;
-    int64_t h2d = 0, d2h = 0;
-    cudaError_t err = cudaSuccess;
-    Staging(rtb_ctx *c, bool h) : ctx(c), host(h) {}
-    ~Staging()
-    {
-        for (void *p : tmp)
-            for (auto &b : ctx->pool) if (b.p == p) b.used = false;
-    }
-    void *alloc(size_t bytes)
-    {
-        if (!bytes) bytes = 8;
-        rtb_ctx::PoolBuf *best = nullptr;
-        for (auto &b : ctx->pool)
-            if (!b.used && b.bytes >= bytes && (!best || b.bytes < best->bytes)) best = &b;
-        if (best && best->bytes <= 2 * bytes + (1 << 20)) {
-            best->used = true;
-            tmp.push_back(best->p);
-            return best->p;
-        }
-        void *d = nullptr;
-        cudaError_t e = cudaMalloc(&d, bytes);
-        if (e != cudaSuccess) { // release idle pool memory and retry once
-            for (auto it = ctx->pool.begin(); it != ctx->pool.end();)
-                if (!it->used) { cudaFree(it->p); it = ctx->pool.erase(it); } else ++it;
-            e = cudaMalloc(&d, bytes);
-        }
-        if (e != cudaSuccess) { err = e; return nullptr; }
-        ctx->pool.push_back({d, bytes, true});
-        tmp.push_back(d);
-        return d;
-    }
-    template <class T> const T *in(const T *p, size_t count)
-    {
-        if (!p || !host) return p;
-        void *d = alloc(count * sizeof(T));
-        if (!d) return nullptr;
-        cudaError_t e = cudaMemcpyAsync(d, p, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream);
-        if (e != cudaSuccess) err = e;
-        h2d += (int64_t)(count * sizeof(T));
-        return (const T *)d;
-    }
-    template <class T> T *out(T *p, size_t count)
-    {
-        if (!p || !host) return p;
-        void *d = alloc(count * sizeof(T));
-        if (!d) return nullptr;
-        back.push_back({p, d, count * sizeof(T)});
-        return (T *)d;
-    }
-    void copy_back()
-    {
-        for (auto &b : back) {
-            cudaError_t e = cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, ctx->stream);
-            if (e != cudaSuccess) err = e;
-            d2h += (int64_t)b.bytes;
-        }
-    }
-};
 
 template <bool EXACT>
 __global__ void field_eval_kernel(DevField f, const DevField *fd, const double *x, const double *y, int64_t n, double *on,

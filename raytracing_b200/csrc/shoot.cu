@@ -1,0 +1,327 @@
+// shoot.cu -- batched two-point shooting search (BASELINE.json configs[4]).
+//
+// The reference has no two-point search (README.md:6 "shooting method" = a forward fan through
+// trazar), so this is DEFINED here from reference parts and is parity-unpinned:
+//   coarse : one fan of A launch angles per DELTA_S candidate is integrated by the trace kernel
+//            (trazar RT_bench.py:766-948); for every target point the angle whose exit point is
+//            closest is the bracket centre (first minimum, like np.argmin);
+//   refine : the launch angle is refined by the reference's own golden-section routine
+//            (golden RT_bench.py:175-199: both probes re-evaluated every iteration, stop when
+//            |c-d| <= GOLD_TOL, result (a+b)/2), one full re-trace of two rays per probe pair,
+//            all (candidate, target) pairs batched into one launch per iteration.
+// "Exit point" of a ray = where its last segment crosses the box of constants() (linear
+// interpolation between the last row inside and the first row outside, RT_bench.py:878), with the
+// travel time s_ray[.,4] interpolated the same way.  miss^2 = squared distance exit point - target.
+#include "ctx.cuh"
+
+namespace {
+
+struct FanBuffers { // device pointers of one batched launch
+    double *theta, *x0, *y0, *steps;
+    int64_t *max_sizes;
+    double *d_ray, *exit_out;
+};
+
+// Launch the integrator on prepared device buffers (FINAL mode + exit points), no staging, no sync.
+int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n, int64_t max_size)
+{
+    TraceArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.f = ctx->f;
+    a.f_dev = ctx->f_dev;
+    a.theta0 = b.theta; a.x0 = b.x0; a.y0 = b.y0;
+    a.steps = b.steps; a.max_sizes = b.max_sizes;
+    a.R = n; a.max_size = (int)max_size; a.out_stride = 1; a.tail_zero = 0;
+    a.step = p->step; a.gamma = p->gamma;
+    a.limx_i = p->limx_i; a.limx_s = p->limx_s; a.limy_i = p->limy_i; a.limy_s = p->limy_s;
+    a.d_ray = b.d_ray;
+    a.exit_out = b.exit_out;
+    a.total_steps = ctx->d_total;
+    // small batches: 32-thread blocks spread the rays over all SMs
+    const int block = n < (int64_t)148 * 4 * 128 ? 32 : ctx->block;
+    cudaError_t e = kLaunch[p->method](a, p->gamma == 1.0, false, (p->flags & RTB_F_EXACT_BASIS) != 0, block, ctx->stream);
+    if (e != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "shoot: trace launch", e);
+    return RTB_OK;
+}
+
+// coarse fan: ray (c, j) = angle j with candidate c's step / max_size
+__global__ void coarse_fill_kernel(const double *angles, int64_t A, const double *steps, const int64_t *max_sizes,
+                                   int64_t C, double sx, double sy, FanBuffers b)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A * C) return;
+    const int64_t c = i / A, j = i - c * A;
+    b.theta[i] = angles[j];
+    b.x0[i] = sx; b.y0[i] = sy;
+    b.steps[i] = steps[c];
+    b.max_sizes[i] = max_sizes[c];
+}
+
+// For each (candidate c, target t): first j minimising |exit(c,j) - target t|^2.
+// grid (ceil(Tn/128), C); exit points of candidate c are staged through shared memory in tiles.
+#define SHOOT_TILE 1024
+__global__ void __launch_bounds__(128) bracket_kernel(const double *exit_out, int64_t A, int64_t C, const double *tx,
+                                                      const double *ty, int64_t Tn, int64_t index0, double *miss2,
+                                                      int64_t *index)
+{
+    __shared__ double sx[SHOOT_TILE], sy[SHOOT_TILE];
+    const int64_t c = blockIdx.y;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const double px = t < Tn ? tx[t] : 0.0, py = t < Tn ? ty[t] : 0.0;
+    const double *ex = exit_out + c * A, *ey = exit_out + A * C + c * A;
+    double best = INFINITY;
+    int64_t bj = 0;
+    for (int64_t j0 = 0; j0 < A; j0 += SHOOT_TILE) {
+        const int m = (int)min((int64_t)SHOOT_TILE, A - j0);
+        for (int k = threadIdx.x; k < m; k += blockDim.x) { sx[k] = ex[j0 + k]; sy[k] = ey[j0 + k]; }
+        __syncthreads();
+        for (int k = 0; k < m; ++k) {
+            const double dx = sx[k] - px, dy = sy[k] - py;
+            const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)); // no contraction: numpy's value
+            if (d2 < best) { best = d2; bj = j0 + k; }
+        }
+        __syncthreads();
+    }
+    if (t < Tn) {
+        miss2[c * Tn + t] = best;
+        index[c * Tn + t] = index0 + bj;
+    }
+}
+
+// golden RT:175-199, state per (candidate, target) pair i: bracket [a,b]; probes c = theta[i], d = theta[n+i].
+__device__ __forceinline__ void golden_probes(double a, double b, double &c, double &d)
+{
+    c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+}
+
+__global__ void refine_init_kernel(const double *lo, const double *hi, const double *steps, const int64_t *max_sizes,
+                                   int64_t Tn, int64_t n, double sx, double sy, double *a, double *b, FanBuffers f,
+                                   unsigned long long *active)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t c = i / Tn;
+    a[i] = lo[i]; b[i] = hi[i];
+    double pc, pd;
+    golden_probes(lo[i], hi[i], pc, pd);
+    const bool act = fabs(pc - pd) > RTB_GOLD_TOL;
+    f.theta[i] = pc; f.theta[n + i] = pd;
+    f.x0[i] = sx; f.x0[n + i] = sx; f.y0[i] = sy; f.y0[n + i] = sy;
+    f.steps[i] = steps[c]; f.steps[n + i] = steps[c];
+    const int64_t m = act ? max_sizes[c] : 1; // converged pairs stop tracing (max_size 1 = no step)
+    f.max_sizes[i] = m; f.max_sizes[n + i] = m;
+    if (act) atomicAdd(active, 1ull);
+}
+
+__global__ void refine_update_kernel(const double *tx, const double *ty, int64_t Tn, int64_t n, double *a, double *b,
+                                     FanBuffers f, unsigned long long *active)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double pc = f.theta[i], pd = f.theta[n + i];
+    if (!(fabs(pc - pd) > RTB_GOLD_TOL)) return; // while abs(c - d) > tol
+    const int64_t t = i % Tn;
+    const double px = tx[t], py = ty[t];
+    const double *ex = f.exit_out, *ey = f.exit_out + 2 * n; // this launch had 2n rays: exit_out is (3, 2n)
+    double dx = ex[i] - px, dy = ey[i] - py;
+    const double fc = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    dx = ex[n + i] - px; dy = ey[n + i] - py;
+    const double fd = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    double va = a[i], vb = b[i];
+    if (fc < fd) vb = pd; else va = pc;
+    a[i] = va; b[i] = vb;
+    double nc, nd;
+    golden_probes(va, vb, nc, nd);
+    f.theta[i] = nc; f.theta[n + i] = nd;
+    if (fabs(nc - nd) > RTB_GOLD_TOL) atomicAdd(active, 1ull);
+    else { f.max_sizes[i] = 1; f.max_sizes[n + i] = 1; }
+}
+
+__global__ void refine_final_fill_kernel(const double *a, const double *b, const int64_t *max_sizes, int64_t Tn,
+                                         int64_t n, double *theta_out, FanBuffers f)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double th = (b[i] + a[i]) / 2.0; // return (b + a) / 2  RT:199
+    theta_out[i] = th;
+    f.theta[i] = th;
+    f.max_sizes[i] = max_sizes[i / Tn];
+}
+
+__global__ void refine_result_kernel(const double *tx, const double *ty, int64_t Tn, int64_t n, FanBuffers f,
+                                     double *result)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t t = i % Tn;
+    // the final launch has n rays: exit_out and d_ray are (3, n)
+    const double ex = f.exit_out[i], ey = f.exit_out[n + i], eT = f.exit_out[2 * n + i];
+    const double dx = ex - tx[t], dy = ey - ty[t];
+    result[i] = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    result[n + i] = eT;
+    result[2 * n + i] = ex;
+    result[3 * n + i] = ey;
+    result[4 * n + i] = f.d_ray[2 * n + i]; // steps taken (integer stored as double, like d_ray[2] RT:890)
+}
+
+} // namespace
+
+static int check_problem(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const char *who)
+{
+    if (!ctx) return RTB_ERR_ARG;
+    if (!ctx->has_field) return fail(ctx, RTB_ERR_NOFIELD, "rtb_shoot: no field set (rtb_set_field)");
+    if (!p || !q || !q->steps || !q->max_sizes || !q->target_x || !q->target_y) return fail(ctx, RTB_ERR_ARG, who);
+    if (p->method < 1 || p->method > 11) return fail(ctx, RTB_ERR_ARG, "rtb_shoot: method must be 1..11");
+    if (q->C < 0 || q->Tn < 0) return fail(ctx, RTB_ERR_ARG, "rtb_shoot: negative size");
+    return RTB_OK;
+}
+
+// max over the candidates' max_sizes (host or device array) = warp-uniform loop bound of the kernel
+static int max_rows(rtb_ctx *ctx, const int64_t *max_sizes, int64_t C, bool host, int64_t *out)
+{
+    std::vector<int64_t> h(C);
+    if (host) std::memcpy(h.data(), max_sizes, sizeof(int64_t) * C);
+    else {
+        CK(cudaMemcpyAsync(h.data(), max_sizes, sizeof(int64_t) * C, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    int64_t m = 1;
+    for (int64_t v : h) {
+        if (v < 1 || v > 0x7fffffff) return fail(ctx, RTB_ERR_ARG, "rtb_shoot: bad max_sizes entry");
+        m = std::max(m, v);
+    }
+    *out = m;
+    return RTB_OK;
+}
+
+static FanBuffers alloc_fan(Staging &sg, int64_t n)
+{
+    FanBuffers b;
+    b.theta = (double *)sg.alloc(sizeof(double) * n);
+    b.x0 = (double *)sg.alloc(sizeof(double) * n);
+    b.y0 = (double *)sg.alloc(sizeof(double) * n);
+    b.steps = (double *)sg.alloc(sizeof(double) * n);
+    b.max_sizes = (int64_t *)sg.alloc(sizeof(int64_t) * n);
+    b.d_ray = (double *)sg.alloc(sizeof(double) * 3 * n);
+    b.exit_out = (double *)sg.alloc(sizeof(double) * 3 * n);
+    return b;
+}
+
+static void finish_stats(rtb_ctx *ctx, rtb_stats *stats, const Staging &sg, unsigned long long total, int64_t launches)
+{
+    if (!stats) return;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); stats->kernel_ms = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); stats->total_ms = ms;
+    stats->ray_steps = (int64_t)total;
+    stats->launches = launches;
+    stats->h2d_bytes = sg.h2d; stats->d2h_bytes = sg.d2h;
+}
+
+extern "C" int rtb_shoot_coarse(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const double *angles,
+                                int64_t A, int64_t index0, double *exit_xyT, double *miss2, int64_t *index,
+                                rtb_stats *stats)
+{
+    int rc = check_problem(ctx, p, q, "rtb_shoot_coarse: null argument");
+    if (rc) return rc;
+    if (!angles || !miss2 || !index || A < 0) return fail(ctx, RTB_ERR_ARG, "rtb_shoot_coarse: null argument");
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    const int64_t C = q->C, Tn = q->Tn, n = C * A;
+    if (n == 0 || Tn == 0) return RTB_OK;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const bool host = p->ptr_kind == RTB_PTR_HOST;
+    int64_t M = 1;
+    if ((rc = max_rows(ctx, q->max_sizes, C, host, &M))) return rc;
+    CK(cudaEventRecord(ctx->ev[0], st));
+    Staging sg(ctx, host);
+    const double *d_ang = sg.in(angles, A), *d_steps = sg.in(q->steps, C);
+    const int64_t *d_msz = sg.in(q->max_sizes, C);
+    const double *d_tx = sg.in(q->target_x, Tn), *d_ty = sg.in(q->target_y, Tn);
+    double *d_miss = sg.out(miss2, C * Tn);
+    int64_t *d_idx = sg.out(index, C * Tn);
+    FanBuffers fb = alloc_fan(sg, n);
+    if (exit_xyT) fb.exit_out = sg.out(exit_xyT, 3 * n);
+    if (sg.err != cudaSuccess || !fb.exit_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_coarse: staging", sg.err);
+    CK(cudaMemsetAsync(ctx->d_total, 0, sizeof(unsigned long long), st));
+    CK(cudaEventRecord(ctx->ev[1], st));
+    coarse_fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_ang, A, d_steps, d_msz, C, q->src_x, q->src_y, fb);
+    if ((rc = launch_fan(ctx, p, fb, n, M))) return rc;
+    bracket_kernel<<<dim3((unsigned)((Tn + 127) / 128), (unsigned)C), 128, 0, st>>>(fb.exit_out, A, C, d_tx, d_ty, Tn,
+                                                                                    index0, d_miss, d_idx);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[2], st));
+    sg.copy_back();
+    unsigned long long total = 0;
+    CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ctx->ev[3], st));
+    CK(cudaStreamSynchronize(st));
+    if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_shoot_coarse: copy", sg.err);
+    finish_stats(ctx, stats, sg, total, 3);
+    return RTB_OK;
+}
+
+extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const double *lo,
+                                const double *hi, double *theta, double *result, int64_t *iterations,
+                                rtb_stats *stats)
+{
+    int rc = check_problem(ctx, p, q, "rtb_shoot_refine: null argument");
+    if (rc) return rc;
+    if (!lo || !hi || !theta || !result) return fail(ctx, RTB_ERR_ARG, "rtb_shoot_refine: null argument");
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    if (iterations) *iterations = 0;
+    const int64_t C = q->C, Tn = q->Tn, n = C * Tn;
+    if (n == 0) return RTB_OK;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const bool host = p->ptr_kind == RTB_PTR_HOST;
+    int64_t M = 1;
+    if ((rc = max_rows(ctx, q->max_sizes, C, host, &M))) return rc;
+    CK(cudaEventRecord(ctx->ev[0], st));
+    Staging sg(ctx, host);
+    const double *d_lo = sg.in(lo, n), *d_hi = sg.in(hi, n), *d_steps = sg.in(q->steps, C);
+    const int64_t *d_msz = sg.in(q->max_sizes, C);
+    const double *d_tx = sg.in(q->target_x, Tn), *d_ty = sg.in(q->target_y, Tn);
+    double *d_theta = sg.out(theta, n), *d_res = sg.out(result, 5 * n);
+    double *d_a = (double *)sg.alloc(sizeof(double) * n), *d_b = (double *)sg.alloc(sizeof(double) * n);
+    unsigned long long *d_active = (unsigned long long *)sg.alloc(sizeof(unsigned long long));
+    FanBuffers fb = alloc_fan(sg, 2 * n);
+    if (sg.err != cudaSuccess || !fb.exit_out || !d_a || !d_b || !d_active)
+        return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_refine: staging", sg.err);
+    CK(cudaMemsetAsync(ctx->d_total, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long), st));
+    CK(cudaEventRecord(ctx->ev[1], st));
+    const unsigned g = (unsigned)((n + 255) / 256);
+    int64_t launches = 1, iters = 0;
+    refine_init_kernel<<<g, 256, 0, st>>>(d_lo, d_hi, d_steps, d_msz, Tn, n, q->src_x, q->src_y, d_a, d_b, fb, d_active);
+    unsigned long long active = 0;
+    CK(cudaMemcpyAsync(&active, d_active, sizeof(active), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    // golden's while loop (RT:188): every pass re-traces both probes of every still-active pair
+    while (active > 0 && iters < 4096) {
+        CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long), st));
+        if ((rc = launch_fan(ctx, p, fb, 2 * n, M))) return rc;
+        refine_update_kernel<<<g, 256, 0, st>>>(d_tx, d_ty, Tn, n, d_a, d_b, fb, d_active);
+        CK(cudaMemcpyAsync(&active, d_active, sizeof(active), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        launches += 2;
+        ++iters;
+    }
+    if (active > 0) return fail(ctx, RTB_ERR_ARG, "rtb_shoot_refine: bracket too wide (no convergence in 4096 iterations)");
+    refine_final_fill_kernel<<<g, 256, 0, st>>>(d_a, d_b, d_msz, Tn, n, d_theta, fb);
+    if ((rc = launch_fan(ctx, p, fb, n, M))) return rc;
+    refine_result_kernel<<<g, 256, 0, st>>>(d_tx, d_ty, Tn, n, fb, d_res);
+    launches += 3;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[2], st));
+    sg.copy_back();
+    unsigned long long total = 0;
+    CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ctx->ev[3], st));
+    CK(cudaStreamSynchronize(st));
+    if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_shoot_refine: copy", sg.err);
+    if (iterations) *iterations = iters;
+    finish_stats(ctx, stats, sg, total, launches);
+    return RTB_OK;
+}

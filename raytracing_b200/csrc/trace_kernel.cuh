@@ -33,6 +33,7 @@ struct TraceArgs {
     double *px_stats;          // (3,R) or nullptr
     const int *cap_rows;       // (2,R) rows to capture (pass 2 of the Snell metric) or nullptr
     double *cap_out;           // (4,R): x_a, y_a, x_b, y_b
+    double *exit_out;          // (3,R) or nullptr: point where the last segment crosses the box, travel time there
     unsigned long long *total_steps;
 };
 
@@ -103,6 +104,9 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
         next_keep = a.out_stride;
     }
 
+    // exit point (two-point shooting search): start of the last segment and the crossing found at exit
+    double pvx = s.x, pvy = s.y, pvT = 0.0, ex_t = 1.0;
+
     bool alive = valid && M > 1;
     int last_i = 0;
     int i = 1;
@@ -113,6 +117,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
         if (!__any_sync(0xffffffffu, alive)) break;
         if (alive) {
             double dist;
+            if (EXTRA) { pvx = s.x; pvy = s.y; pvT = T; }
             if (EXACT) {
                 double fx, fy, fang, fn, fgx, fgy;
                 if (METHOD == 7 && i < 3) { // bootstrap RT:838-864
@@ -164,7 +169,17 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
             }
             // boundary test RT:878 (strict)
-            if (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i) alive = false;
+            if (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i) {
+                alive = false;
+                if (EXTRA) { // fraction of the last segment inside the box (first limit crossed)
+                    double t = 1.0;
+                    if (s.x > a.limx_s) t = fmin(t, (a.limx_s - pvx) / (s.x - pvx));
+                    if (s.x < a.limx_i) t = fmin(t, (a.limx_i - pvx) / (s.x - pvx));
+                    if (s.y > a.limy_s) t = fmin(t, (a.limy_s - pvy) / (s.y - pvy));
+                    if (s.y < a.limy_i) t = fmin(t, (a.limy_i - pvy) / (s.y - pvy));
+                    ex_t = fmax(t, 0.0);
+                }
+            }
             if (i + 1 >= M) alive = false;
             if (TRAJ && i == next_keep) {
                 store_row(sp, a.R, s.x, s.y, px, py, T, s.ang);
@@ -214,6 +229,11 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
             a.px_stats[a.R + r] = mean;
             a.px_stats[2 * a.R + r] = sd;
         }
+        if (EXTRA && a.exit_out) { // a ray that never left the box reports its last position (ex_t == 1)
+            a.exit_out[r] = pvx + ex_t * (s.x - pvx);
+            a.exit_out[a.R + r] = pvy + ex_t * (s.y - pvy);
+            a.exit_out[2 * a.R + r] = pvT + ex_t * (T - pvT);
+        }
         if (EXTRA && !TRAJ && a.cap_out) {
             a.cap_out[r] = capv[0]; a.cap_out[a.R + r] = capv[1];
             a.cap_out[2 * a.R + r] = capv[2]; a.cap_out[3 * a.R + r] = capv[3];
@@ -234,7 +254,7 @@ template <int METHOD>
 cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
 {
     const unsigned grid = (unsigned)((a.R + block - 1) / block);
-    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr;
+    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr;
 #define RTB_L(I, T, E)                                                                  \
     do {                                                                                \
         if (extra) trace_kernel<METHOD, I, T, E, true><<<grid, block, 0, st>>>(a);      \

@@ -186,3 +186,64 @@ class Engine:
         return TraceResult(s_ray=s_ray, d_ray=d_ray, errors=errors, last_row=last_row, px_stats=px_stats,
                            stats=dict(kernel_ms=stats.kernel_ms, total_ms=stats.total_ms, ray_steps=stats.ray_steps,
                                       launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes))
+
+    # -- batched two-point shooting search (include/rtb.h rtb_shoot_*; parity-unpinned) --
+    def _shoot_args(self, method, src, steps, max_sizes, targets, gamma, box, exact, like):
+        """Common marshalling: arrays follow `like` (torch CUDA tensor -> device pointers, else host)."""
+        dev = _is_torch(like)
+        if dev:
+            import torch
+            f64 = lambda a: a.contiguous() if _is_torch(a) else torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).to(like.device)
+            i64 = lambda a: a if _is_torch(a) else torch.as_tensor(np.ascontiguousarray(a, dtype=np.int64)).to(like.device)
+            ptr = lambda a: C.c_void_p(a.data_ptr()) if a is not None else None
+            empty = lambda shape, dt=None: torch.empty(*shape, dtype=dt or torch.float64, device=like.device)
+            i64t = torch.int64
+        else:
+            f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+            i64 = lambda a: np.ascontiguousarray(a, dtype=np.int64)
+            ptr = lambda a: C.c_void_p(a.ctypes.data) if a is not None else None
+            empty = lambda shape, dt=None: np.empty(shape, dtype=dt or np.float64)
+            i64t = np.int64
+        steps, max_sizes = f64(steps), i64(max_sizes)
+        tx, ty = f64(targets[0]), f64(targets[1])
+        Cn, Tn = int(steps.shape[0]), int(tx.shape[0])
+        flags = _cabi.RTB_F_EXACT_BASIS if exact else 0
+        p = _cabi.RtbParams(method_id(method), flags, _cabi.RTB_PTR_DEVICE if dev else _cabi.RTB_PTR_HOST, 1, 1,
+                            float(gamma), 0.0, float(box[0]), float(box[1]), float(box[2]), float(box[3]), None, None)
+        q = _cabi.RtbShootProblem(float(src[0]), float(src[1]), ptr(steps), ptr(max_sizes), Cn, ptr(tx), ptr(ty), Tn)
+        keep = (steps, max_sizes, tx, ty)
+        return p, q, Cn, Tn, f64, ptr, empty, i64t, keep
+
+    @staticmethod
+    def _stats(stats):
+        return dict(kernel_ms=stats.kernel_ms, total_ms=stats.total_ms, ray_steps=stats.ray_steps,
+                    launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes)
+
+    def shoot_coarse(self, method, angles, src, steps, max_sizes, targets, gamma, box, index0=0, want_exit=False,
+                     exact=False):
+        """Coarse phase: trace the fan `angles` for every DELTA_S candidate and bracket every target.
+        Returns TraceResult(miss2 (C,Tn), index (C,Tn) int64, exit (3,C,A) or None, stats)."""
+        p, q, Cn, Tn, f64, ptr, empty, i64t, keep = self._shoot_args(method, src, steps, max_sizes, targets, gamma, box,
+                                                                     exact, angles)
+        angles = f64(angles)
+        A = int(angles.shape[0])
+        miss2, index = empty((Cn, Tn)), empty((Cn, Tn), i64t)
+        ex = empty((3, Cn, A)) if want_exit else None
+        stats = _cabi.RtbStats()
+        self._check(self._lib.rtb_shoot_coarse(self._ctx, C.byref(p), C.byref(q), ptr(angles), A, int(index0), ptr(ex),
+                                               ptr(miss2), ptr(index), C.byref(stats)))
+        return TraceResult(miss2=miss2, index=index, exit=ex, stats=self._stats(stats))
+
+    def shoot_refine(self, method, lo, hi, src, steps, max_sizes, targets, gamma, box, exact=False):
+        """golden(miss^2, lo, hi) (RT_bench.py:175-199) for every (candidate, target) pair.
+        Returns TraceResult(theta (C,Tn), result (5,C,Tn) = miss, T, exit x, exit y, steps; iterations; stats)."""
+        p, q, Cn, Tn, f64, ptr, empty, i64t, keep = self._shoot_args(method, src, steps, max_sizes, targets, gamma, box,
+                                                                     exact, lo)
+        lo, hi = f64(lo), f64(hi)
+        assert tuple(lo.shape) == (Cn, Tn) and tuple(hi.shape) == (Cn, Tn)
+        theta, result = empty((Cn, Tn)), empty((5, Cn, Tn))
+        it = C.c_int64(0)
+        stats = _cabi.RtbStats()
+        self._check(self._lib.rtb_shoot_refine(self._ctx, C.byref(p), C.byref(q), ptr(lo), ptr(hi), ptr(theta),
+                                               ptr(result), C.byref(it), C.byref(stats)))
+        return TraceResult(theta=theta, result=result, iterations=it.value, stats=self._stats(stats))

@@ -1,12 +1,13 @@
 """Generate the golden fixtures in tests/golden/ from the UNMODIFIED reference.
 
 Runs only in the build container (needs /root/reference); the fixtures are committed so the
-tests run anywhere.  Usage:  python tests/golden/gen_golden.py [traj|field|sweep|sens|all]
+tests run anywhere.  Usage:  python tests/golden/gen_golden.py [traj|field|sweep|sens|shoot|all]
 
   ref_traj.npz    trazar outputs of every (scenario, method) on the default fans (d_ray, errors,
                   strided s_ray rows, last row per ray) and on slices of the synthetic fans
   ref_field.npz   n_gradient at random points and next to knots, per scenario
   ref_sweep.npz   search_delta metrics over the DELTA_S sweep + find_index result (RT:1303-1385)
+  ref_shoot.npz   two-point shooting problems solved with RT.trazar rays + RT.golden refinement
   sensitivity.json  the reference algorithm's response to +-1 ulp sin/cos noise (oracle probe,
                   cross-checked against the same probe on the real reference for a few cases)
 """
@@ -163,6 +164,58 @@ def gen_sens():
     json.dump(out, open(os.path.join(HERE, "sensitivity.json"), "w"), indent=1)
 
 
+def _shoot_task(args):
+    """Two-point search (oracle/shoot_oracle.py procedure) with every ray traced by the REAL RT.trazar and
+    the refinement done by the REAL RT.golden."""
+    uc, m, div, true_angles, A = args
+    from oracle import shoot_oracle as S
+    RT = L.load_reference()
+    fan = dict(theta_v=np.zeros(1))
+    z, grd = L.setup_scenario(RT, uc, fan)
+    step = RT.SIGMA / div
+    box = (RT.limx_i, RT.limx_s, RT.limy_i, RT.limy_s)
+
+    def trace_fn(th):
+        fan["theta_v"] = np.asarray(th, dtype=np.float64)
+        s, d, _ct, _e = RT.trazar(L.method(RT, m), z, grd, False, step, RT.DELTA_S_DIVISOR_FISHEYE + 1, uc)
+        return s, d
+    tr = S.Tracer(m, z, grd, step, 0, RT.gamma, box, (-2.0, -2.0), trace_fn=trace_fn)
+    lo_a = 2 * np.pi / 60 if uc == "1" else 0.0
+    angles = np.linspace(lo_a, np.pi / 2, A)
+    e_true, _ = tr(true_angles)
+    tx, ty = e_true[0], e_true[1]
+    ex, ns = tr(angles)
+    out = dict(angles=angles, true_angles=np.asarray(true_angles), tx=tx, ty=ty, T_true=e_true[2], step=np.float64(step),
+               coarse_exit=ex, coarse_nsteps=ns)
+    res = {k: [] for k in ("theta", "miss", "T", "exit_x", "exit_y", "nsteps", "index")}
+    for t in range(len(tx)):
+        m2 = (ex[0] - tx[t]) ** 2 + (ex[1] - ty[t]) ** 2
+        j = int(np.argmin(m2))
+        lo, hi = angles[max(j - 1, 0)], angles[min(j + 1, A - 1)]
+        f = lambda th: float(((tr([th])[0][:2, 0] - np.array([tx[t], ty[t]])) ** 2).sum())
+        theta = RT.golden(f, lo, hi)
+        e, n1 = tr([theta])
+        for k, v in zip(res, (theta, np.hypot(e[0, 0] - tx[t], e[1, 0] - ty[t]), e[2, 0], e[0, 0], e[1, 0], n1[0], j)):
+            res[k].append(v)
+    out.update({k: np.array(v) for k, v in res.items()})
+    return "s%s_op%d" % (uc, m), out
+
+
+def gen_shoot():
+    """ref_shoot.npz: small two-point problems solved through the real reference (parity anchor of the
+    parts; the procedure itself is ours, see oracle/shoot_oracle.py)."""
+    tasks = [("1", 6, 3.0, np.array([0.3, 0.6, 0.9, 1.0, 1.2, 1.4]) + 0.00371, 64),
+             ("1", 8, 2.0, np.array([0.5, 1.1, 1.3]) + 0.00113, 48),
+             ("3", 8, 2.0, np.array([0.4, 0.9, 1.3]) + 0.00229, 48)]
+    flat = {}
+    with Pool(3) as pool:
+        for key, d in pool.imap_unordered(_shoot_task, tasks):
+            print("shoot", key, d["theta"] - d["true_angles"], d["miss"], flush=True)
+            for k, v in d.items():
+                flat[key + "/" + k] = v
+    np.savez_compressed(os.path.join(HERE, "ref_shoot.npz"), **flat)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("sens", "all"):
@@ -173,3 +226,5 @@ if __name__ == "__main__":
         gen_traj()
     if what in ("sweep", "all"):
         gen_sweep()
+    if what in ("shoot", "all"):
+        gen_shoot()
