@@ -15,7 +15,7 @@ reference parts and is parity-unpinned:
 
 Everything numeric runs in librtb.so (rtb_shoot_coarse / rtb_shoot_refine); this module only slices
 arrays and, across GPUs, reduces the coarse (miss^2, index) pairs with MIN (torch.distributed).
-oracle/shoot_oracle.py restates the same procedure on the CPU for the tests.
+The tests hold a CPU restatement of the same procedure (test infrastructure, never imported here).
 """
 import numpy as np
 
