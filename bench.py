@@ -285,7 +285,15 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-full", action="store_true", help="skip the FULL-trajectory (45.8 GB s_ray) leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="fisheye", choices=["fisheye", "vert", "aniso", "shoot"],
+                    help="fisheye = the headline configs[1] line (default); vert / aniso / shoot = configs[2..4], "
+                         "run by tools/bench_configs.py")
     args = ap.parse_args()
+    if args.workload != "fisheye" and args.impl == "cuda":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_configs
+        return bench_configs.main(["--workload", args.workload, "--gpus", str(args.gpus), "--steps", str(args.steps),
+                                   "--warmup", str(args.warmup)])
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -14,6 +14,16 @@ def shard_bounds(R, world, rank):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def cyclic_indices(R, world, rank, block=4096):
+    """Block-cyclic ownership: rank r owns blocks r, r+world, r+2*world, ... of `block` consecutive rays.
+    Rays of a fan sorted by launch angle differ 3x in step count; contiguous shards would
+    leave the ranks unevenly loaded, interleaved blocks give every rank the same mix."""
+    nb = (int(R) + block - 1) // block
+    mine = np.arange(rank, nb, world, dtype=np.int64)
+    idx = (mine[:, None] * block + np.arange(block, dtype=np.int64)[None, :]).ravel()
+    return idx[idx < R]
+
+
 def gather_rays(local, R, group=None):
     """All-gather a per-ray tensor (..., R_local) from every rank into (..., R) (ragged shards ok)."""
     import torch
