@@ -56,6 +56,23 @@ __constant__ double kCos[6] = {-1.13596475577881948265e-11, 2.087572321298174827
 __constant__ double kPio2[4] = {6.36619772367581382433e-01, -1.57079632673412561417e+00, -6.07710050630396597660e-11,
                                 -2.02226624879595063154e-21};
 
+// Other non-"round" constants of the step loop (a 64-bit immediate costs two UMOV/IMAD.MOV issue slots at every
+// use; as c[bank][offset] operands they are free).  Constants whose low word is zero (0.5, 1, 0.75 ...) encode
+// as 32-bit immediates and stay literal.
+__constant__ double kK[6] = {1.0 / 6.0, 2.0 / 3.0, 1.0 / 24.0, 1.0 / 120.0, -1.0 / 5040.0, -1.0 / 720.0};
+#define K_SIXTH kK[0]
+#define K_TWOTHIRDS kK[1]
+#define K_1_24 kK[2]
+#define K_1_120 kK[3]
+#define K_M1_5040 kK[4]
+#define K_M1_720 kK[5]
+
+// |x| < 2^e-ish threshold tests on the high word: integer compare, keeps the FP64 pipe for arithmetic.
+__device__ __forceinline__ bool abs_lt_hi(double x, int hi_word) { return (__double2hiint(x) & 0x7fffffff) < hi_word; }
+#define HI_0_75 0x3fe80000   // 0.75
+#define HI_2M20 0x3eb00000   // 2^-20 = 9.54e-7
+#define HI_2M11 0x3f400000   // 2^-11 = 4.88e-4
+
 // sin/cos kernels on |r| <= pi/4 (+ slack), minimax-quality Taylor coefficients in Horner form.
 __device__ __forceinline__ double sin_kernel(double r, double r2)
 {
@@ -81,7 +98,7 @@ __device__ __forceinline__ double cos_kernel(double r2)
 }
 
 // sin and cos of a small increment |k| <= SMALL_ANGLE_MAX without range reduction.
-#define RTB_SMALL_ANGLE_MAX 0.7
+#define RTB_SMALL_ANGLE_MAX 0.75
 __device__ __forceinline__ void sincos_small(double k, double &s, double &c)
 {
     const double k2 = k * k;
@@ -109,12 +126,12 @@ __device__ __forceinline__ void rotate(double s0, double c0, double k, double &s
 {
     const double k2 = k * k;
     double sk, cm; // sin k, cos k - 1
-    if (k2 < 1.0e-6) {
-        sk = fma(k * k2, -1.0 / 6.0, k);
-        cm = k2 * fma(k2, 1.0 / 24.0, -0.5);
-    } else if (k2 < 4.0e-4) {
-        sk = fma(k * k2, fma(k2, fma(k2, -1.0 / 5040.0, 1.0 / 120.0), -1.0 / 6.0), k);
-        cm = k2 * fma(k2, fma(k2, -1.0 / 720.0, 1.0 / 24.0), -0.5);
+    if (abs_lt_hi(k2, HI_2M20)) {          // |k| < 9.8e-4: truncation < 1e-17
+        sk = fma(k * k2, -K_SIXTH, k);
+        cm = k2 * fma(k2, K_1_24, -0.5);
+    } else if (abs_lt_hi(k2, HI_2M11)) {   // |k| < 2.2e-2: truncation < 2e-18
+        sk = fma(k * k2, fma(k2, fma(k2, K_M1_5040, K_1_120), -K_SIXTH), k);
+        cm = k2 * fma(k2, fma(k2, K_M1_720, K_1_24), -0.5);
     } else {
         sk = sin_kernel(k, k2);
         double p = kCos[0];

@@ -13,6 +13,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "fastmath.cuh"
 
 namespace rtb {
 
@@ -24,6 +25,7 @@ struct DevAxis {
     int lo, hi;       // inclusive range of l (0-based, t[l] <= x < t[l+1]) where t[l-k+1 .. l+k] is uniform
     double t0, inv_h; // origin and reciprocal nominal spacing of the interior knots
     double tb, te;    // clamp range t[k], t[n-k-1]  (fpbisp: arg clamped to [tb, te])
+    double c0;        // off - t0*inv_h - 0.5: fma(x, inv_h, c0) = (interval coordinate) - 0.5 on the uniform run
 };
 
 struct DevField {
@@ -82,12 +84,11 @@ __device__ __forceinline__ void basis_exact(const double *__restrict__ t, int l,
 __device__ __forceinline__ void basis_uniform3(double s, double *w)
 {
     const double s2 = s * s, s3 = s2 * s;
-    const double sixth = 1.0 / 6.0;
     const double om = 1.0 - s;
-    w[0] = om * om * om * sixth;
-    w[1] = fma(s3, 0.5, fma(s2, -1.0, 2.0 / 3.0));
-    w[2] = fma(s3, -0.5, fma(s2, 0.5, fma(s, 0.5, sixth)));
-    w[3] = s3 * sixth;
+    w[0] = om * om * (om * K_SIXTH);
+    w[1] = fma(s3, 0.5, fma(s2, -1.0, K_TWOTHIRDS));
+    w[2] = fma(s3, -0.5, fma(s2, 0.5, fma(s, 0.5, K_SIXTH)));
+    w[3] = s3 * K_SIXTH;
 }
 
 template <bool EXACT>
@@ -170,15 +171,24 @@ static __device__ __noinline__ FieldSample n_gradient_general(const DevField *fd
 __device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevField *fd, double x, double y,
                                                 double &n, double &gx, double &gy)
 {
-    const int lu = __double2int_rd((y - f.gu_.t0) * f.gu_.inv_h) + f.gu_.off;
-    const int lv = __double2int_rd((x - f.gv_.t0) * f.gv_.inv_h) + f.gv_.off;
-    if (!f.fast_ok || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
+    // Interval index and cell fraction without conversion instructions or knot loads: vh = (interval
+    // coordinate) - 0.5; adding 1.5*2^52 rounds it to the nearest integer = floor(coordinate), which then sits in
+    // the low word of the sum; the fraction is vh - that integer + 0.5.  (A coordinate within half an ulp of a
+    // knot may land in the neighbouring cell with fraction 1 or 0: same value, the spline is continuous.)
+    // The knots of the uniform run equal t0 + j/inv_h to < 3e-13 of a cell (checked in rtb_set_field).
+    const double MAGIC = 6755399441055744.0;
+    const double vu = fma(y, f.gu_.inv_h, f.gu_.c0), vv = fma(x, f.gv_.inv_h, f.gv_.c0);
+    const double mu = vu + MAGIC, mv = vv + MAGIC;
+    const int lu = __double2loint(mu), lv = __double2loint(mv);
+    // |coordinate| < 2^31 <=> high word of the sum is 0x43380000 (or 0x4337ffff for negatives); NaN fails too
+    const bool sane = (unsigned)(__double2hiint(mu) - 0x4337ffff) <= 1u && (unsigned)(__double2hiint(mv) - 0x4337ffff) <= 1u;
+    if (!f.fast_ok || !sane || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
         const FieldSample r = n_gradient_general(fd, x, y);
         n = r.n; gx = r.gx; gy = r.gy;
         return;
     }
-    const double su = (y - __ldg(f.gu_.t + lu)) * f.gu_.inv_h;
-    const double sv = (x - __ldg(f.gv_.t + lv)) * f.gv_.inv_h;
+    const double su = (vu - (mu - MAGIC)) + 0.5;
+    const double sv = (vv - (mv - MAGIC)) + 0.5;
     {
         const double *c = f.cz + (size_t)(lu - 2) * f.ncz + (lv - 2); // bilinear l = cubic l - 1
         const double c00 = __ldg(c), c01 = __ldg(c + 1), c10 = __ldg(c + f.ncz), c11 = __ldg(c + f.ncz + 1);

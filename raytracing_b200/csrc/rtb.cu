@@ -101,6 +101,13 @@ static int make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax)
     } else {
         ax->t0 = t[k]; ax->off = k; ax->lo = 1; ax->hi = 0;
     }
+    ax->c0 = (double)ax->off - ax->t0 * ax->inv_h - 0.5;
+    // the default evaluator takes the cell fraction from t0 + j/inv_h instead of the stored knots: allowed only if
+    // they agree to 1e-12 of a cell over the uniform run (linspace knots: ~2e-13), else the run is disabled
+    for (int l = ax->lo; l <= ax->hi + 1 && ax->hi >= ax->lo; ++l) {
+        const double dev = (t[l] - ax->t0) * ax->inv_h - (double)(l - ax->off);
+        if (std::fabs(dev) > 1e-12) { ax->lo = 1; ax->hi = 0; break; }
+    }
     return RTB_OK;
 }
 

@@ -145,13 +145,14 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
     } else if (UPD == 2) { // tfinal_2o RT:374-391
         const double k1 = h * (s.ux * s.gy - s.uy * s.gx) * s.inv_n;
         double s1, c1;
-        if (fabs(k1) <= RTB_SMALL_ANGLE_MAX) rotate(s.uy, s.ux, k1, s1, c1);
+        const bool small1 = abs_lt_hi(k1, HI_0_75);
+        if (small1) rotate(s.uy, s.ux, k1, s1, c1);
         else sincos_cw(s.ang + k1, s1, c1);
         const double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
         const double kf = 0.5 * (k1 + k2);
         s.ang += kf;
         // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
-        if (fabs(k1) <= RTB_SMALL_ANGLE_MAX && fabs(kf) <= RTB_SMALL_ANGLE_MAX && (i & RTB_RESYNC_MASK) != 0) {
+        if (small1 && abs_lt_hi(kf, HI_0_75) && (i & RTB_RESYNC_MASK) != 0) {
             rotate(s1, c1, 0.5 * (k2 - k1), s.uy, s.ux);
         } else {
             sincos_cw(s.ang, s.uy, s.ux);

@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             } else {
                 dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3);
-                moments_fast<ISO>(s, g2m1, px, py);
+                if (TRAJ || EXTRA) moments_fast<ISO>(s, g2m1, px, py); // else only the last row's, after the loop
             }
             dist_sim += dist;
             dist_real += h;
@@ -169,8 +169,8 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
             }
             // boundary test RT:878 (strict)
-            if (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i) {
-                alive = false;
+            const bool outside = s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i;
+            if (outside) {
                 if (EXTRA) { // fraction of the last segment inside the box (first limit crossed)
                     double t = 1.0;
                     if (s.x > a.limx_s) t = fmin(t, (a.limx_s - pvx) / (s.x - pvx));
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                     ex_t = fmax(t, 0.0);
                 }
             }
-            if (i + 1 >= M) alive = false;
+            alive = !outside && i + 1 < M;
             if (TRAJ && i == next_keep) {
                 store_row(sp, a.R, s.x, s.y, px, py, T, s.ang);
                 sp += 6 * a.R;
@@ -204,6 +204,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
         }
     }
     if (LAZY && s.ang != s.ang) s.ang = atan2(s.uy, s.ux); // theta of the last row (NaN = not evaluated yet)
+    if (!EXACT && !TRAJ && !EXTRA && last_i > 0) moments_fast<ISO>(s, g2m1, px, py);
 
     // per-ray results RT:888-890
     if (valid) {
