@@ -72,6 +72,7 @@ __device__ __forceinline__ bool abs_lt_hi(double x, int hi_word) { return (__dou
 #define HI_0_75 0x3fe80000   // 0.75
 #define HI_2M20 0x3eb00000   // 2^-20 = 9.54e-7
 #define HI_2M11 0x3f400000   // 2^-11 = 4.88e-4
+#define HI_2M6 0x3f900000    // 2^-6 = 1.5625e-2
 
 // sin/cos kernels on |r| <= pi/4 (+ slack), minimax-quality Taylor coefficients in Horner form.
 __device__ __forceinline__ double sin_kernel(double r, double r2)
@@ -142,6 +143,17 @@ __device__ __forceinline__ void rotate(double s0, double c0, double k, double &s
         p = fma(p, k2, kCos[5]);
         cm = fma(k2 * k2, p, -0.5 * k2);
     }
+    s = s0 + fma(s0, cm, c0 * sk);
+    c = c0 + fma(c0, cm, -(s0 * sk));
+}
+
+// Branch-free rotation for |k| < 2^-6: sin k to k^7 (next term k^9/362880 < 5e-22), cos k - 1 to k^6 (next
+// term k^8/40320 < 9e-20).
+__device__ __forceinline__ void rotate_mid(double s0, double c0, double k, double &s, double &c)
+{
+    const double k2 = k * k;
+    const double sk = fma(k * k2, fma(k2, fma(k2, K_M1_5040, K_1_120), -K_SIXTH), k);
+    const double cm = k2 * fma(k2, fma(k2, K_M1_720, K_1_24), -0.5);
     s = s0 + fma(s0, cm, c0 * sk);
     c = c0 + fma(c0, cm, -(s0 * sk));
 }

@@ -143,20 +143,28 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         s.ux = a * r; s.uy = b * r;
         s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux);
     } else if (UPD == 2) { // tfinal_2o RT:374-391
+        // Straight-line form: both rotations use the fixed mid-degree polynomial (valid for |k| < 2^-6, every
+        // per-step increment in practice) so the whole update is one basic block the scheduler can interleave
+        // with the reciprocal / square-root chains; the rare cases (large curvature*step) and the periodic exact
+        // resync of (sin, cos) with the accumulated angle are repaired in ONE conditional block afterwards.
         const double k1 = h * (s.ux * s.gy - s.uy * s.gx) * s.inv_n;
         double s1, c1;
-        const bool small1 = abs_lt_hi(k1, HI_0_75);
-        if (small1) rotate(s.uy, s.ux, k1, s1, c1);
-        else sincos_cw(s.ang + k1, s1, c1);
-        const double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
-        const double kf = 0.5 * (k1 + k2);
-        s.ang += kf;
+        rotate_mid(s.uy, s.ux, k1, s1, c1);
+        double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
+        double ang = s.ang + 0.5 * (k1 + k2);
+        double nuy, nux;
         // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
-        if (small1 && abs_lt_hi(kf, HI_0_75) && (i & RTB_RESYNC_MASK) != 0) {
-            rotate(s1, c1, 0.5 * (k2 - k1), s.uy, s.ux);
-        } else {
-            sincos_cw(s.ang, s.uy, s.ux);
+        rotate_mid(s1, c1, 0.5 * (k2 - k1), nuy, nux);
+        const bool small = abs_lt_hi(k1, HI_2M6) && abs_lt_hi(k2, HI_2M6);
+        if (!small || (i & RTB_RESYNC_MASK) == 0) {
+            if (!small) {
+                sincos_cw(s.ang + k1, s1, c1);
+                k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
+                ang = s.ang + 0.5 * (k1 + k2);
+            }
+            sincos_cw(ang, nuy, nux);
         }
+        s.ang = ang; s.uy = nuy; s.ux = nux;
     } else if (UPD == 4) { // golden, isotropic cost RT:595,697
         CostIsoFast cf;
         cf.n1 = fn;
