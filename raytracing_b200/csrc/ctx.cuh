@@ -54,6 +54,21 @@ static inline int fail(rtb_ctx *c, int code, const char *what, cudaError_t e = c
         if (e_ != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, #call, e_);     \
     } while (0)
 
+// Cells of the default evaluator's fast region that lie strictly inside the box (two cells of margin cover the
+// half-ulp slop of the device-side index): a position indexed into them needs no FP64 box compares.
+static inline CellBox make_cell_box(const DevField &f, double limx_i, double limx_s, double limy_i, double limy_s)
+{
+    CellBox b = {1, 0, 1, 0};
+    if (!f.fast_ok) return b;
+    auto coord = [](const DevAxis &a, double x) { return std::floor(x * a.inv_h + a.c0 + 0.5); };
+    auto clampi = [](double v) { return (int)std::max(-1.0e9, std::min(1.0e9, v)); };
+    b.lo_u = std::max(f.flo_u, clampi(coord(f.gu_, limy_i) + 2));
+    b.hi_u = std::min(f.fhi_u, clampi(coord(f.gu_, limy_s) - 2));
+    b.lo_v = std::max(f.flo_v, clampi(coord(f.gv_, limx_i) + 2));
+    b.hi_v = std::min(f.fhi_v, clampi(coord(f.gv_, limx_s) - 2));
+    return b;
+}
+
 // ---------------------------------------------------------------------------------------
 // Staging: with RTB_PTR_HOST the library owns temporary device buffers for the call.
 // ---------------------------------------------------------------------------------------

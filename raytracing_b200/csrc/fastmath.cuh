@@ -14,13 +14,24 @@ namespace rtb {
 // MUFU.RCP64H seed (~20 bits) + two Newton steps -> < 1 ulp.
 __device__ __forceinline__ double rcp_fast(double x)
 {
+    // MUFU.RCP64H seed (relative error e0 ~ 2^-20), one cubically convergent step r(1 + e + e^2), then one
+    // residual correction: error ~e0^3 = 2^-60 before the final rounding (< 1 ulp), 4 DFMA like two Newton steps
+    // but the last one makes the result accurate to the last bit in all but ~1e-3 of the cases
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
     double e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
+    r = fma(r, fma(e, e, e), r);
     e = fma(-x, r, 1.0);
-    r = fma(r, e, r);
-    return r;
+    return fma(r, e, r);
+}
+
+// 1/x to < 1 ulp in 3 DFMA (no final residual step): the step loop's reciprocals of n.
+__device__ __forceinline__ double rcp_fast3(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = fma(-x, r, 1.0);
+    return fma(r, fma(e, e, e), r);
 }
 
 // 1/sqrt(x) for normal x > 0: MUFU.RSQ64H seed + two Newton steps.
@@ -73,6 +84,7 @@ __device__ __forceinline__ bool abs_lt_hi(double x, int hi_word) { return (__dou
 #define HI_2M20 0x3eb00000   // 2^-20 = 9.54e-7
 #define HI_2M11 0x3f400000   // 2^-11 = 4.88e-4
 #define HI_2M6 0x3f900000    // 2^-6 = 1.5625e-2
+#define HI_2M8 0x3f700000    // 2^-8 = 3.90625e-3
 
 // sin/cos kernels on |r| <= pi/4 (+ slack), minimax-quality Taylor coefficients in Horner form.
 __device__ __forceinline__ double sin_kernel(double r, double r2)
@@ -111,13 +123,14 @@ __device__ __forceinline__ void sincos_small(double k, double &s, double &c)
 // residual correction of the product (-> < 1 ulp).
 __device__ __forceinline__ double sqrt_pos(double x)
 {
+    // y0 = MUFU.RSQ64H seed (e0 ~ 2^-20); y = y0 (1 + e/2 + 3e^2/8) with e = 1 - x y0^2 leaves ~e0^3 = 2^-60;
+    // sqrt(x) = x * y, < 1 ulp.  6 FP64 instructions (two Newton steps + residual correction: 8).
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
     const double e = fma(-x * y, y, 1.0);
-    y = fma(0.5 * y, e, y);
-    double s = x * y;
-    const double r = fma(-s, s, x);
-    return fma(r, 0.5 * y, s);
+    const double t = fma(e, 0.375, 0.5) * e;
+    y = fma(y, t, y);
+    return x * y;
 }
 
 // (sin, cos)(theta + k) from (s0, c0) = (sin, cos)(theta) by the angle-addition formulas, written as
@@ -147,13 +160,13 @@ __device__ __forceinline__ void rotate(double s0, double c0, double k, double &s
     c = c0 + fma(c0, cm, -(s0 * sk));
 }
 
-// Branch-free rotation for |k| < 2^-6: sin k to k^7 (next term k^9/362880 < 5e-22), cos k - 1 to k^6 (next
-// term k^8/40320 < 9e-20).
-__device__ __forceinline__ void rotate_mid(double s0, double c0, double k, double &s, double &c)
+// Branch-free rotation for |k| < 2^-8: sin k to k^5 (next term k^7/5040 < 3e-21), cos k - 1 to k^4 (next term
+// k^6/720 < 5e-18).
+__device__ __forceinline__ void rotate_small(double s0, double c0, double k, double &s, double &c)
 {
     const double k2 = k * k;
-    const double sk = fma(k * k2, fma(k2, fma(k2, K_M1_5040, K_1_120), -K_SIXTH), k);
-    const double cm = k2 * fma(k2, fma(k2, K_M1_720, K_1_24), -0.5);
+    const double sk = fma(k * k2, fma(k2, K_1_120, -K_SIXTH), k);
+    const double cm = k2 * fma(k2, K_1_24, -0.5);
     s = s0 + fma(s0, cm, c0 * sk);
     c = c0 + fma(c0, cm, -(s0 * sk));
 }

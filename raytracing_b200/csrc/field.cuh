@@ -42,6 +42,11 @@ struct DevField {
     int fast_ok, flo_u, fhi_u, flo_v, fhi_v;
 };
 
+// Cubic-interval index ranges (inclusive) inside which a position needs no further checks in the step loop:
+// the default evaluator's fast region intersected with the cells that lie strictly inside the box of
+// constants() (RT:878), so the common case pays neither the general-path test nor the four FP64 box compares.
+struct CellBox { int lo_u, hi_u, lo_v, hi_v; };
+
 // FITPACK fpbisp interval search, restated for the GPU: clamp, then find l (0-based) with
 // t[l] <= x < t[l+1], k <= l <= n-k-2.  FITPACK walks linearly from l=k; here a
 // multiply+floor guess is corrected against the real knots, which yields the same l.
@@ -83,12 +88,14 @@ __device__ __forceinline__ void basis_exact(const double *__restrict__ t, int l,
 // Closed-form uniform cubic B-spline basis at s = (x - t[l]) / h in [0,1).
 __device__ __forceinline__ void basis_uniform3(double s, double *w)
 {
+    // 10 FP64 instructions: w3 = s^3/6, p = w0 + w3 = 1/6 - s/2 + s^2/2, w1 = 2/3 - s^2 + s^3/2, and the
+    // partition of unity for w2 (weights are O(1): the subtractions cost ~1e-16 absolute)
     const double s2 = s * s, s3 = s2 * s;
-    const double om = 1.0 - s;
-    w[0] = om * om * (om * K_SIXTH);
-    w[1] = fma(s3, 0.5, fma(s2, -1.0, K_TWOTHIRDS));
-    w[2] = fma(s3, -0.5, fma(s2, 0.5, fma(s, 0.5, K_SIXTH)));
     w[3] = s3 * K_SIXTH;
+    const double p = fma(s2, 0.5, fma(s, -0.5, K_SIXTH));
+    w[0] = p - w[3];
+    w[1] = fma(s3, 0.5, K_TWOTHIRDS - s2);
+    w[2] = (1.0 - p) - w[1];
 }
 
 template <bool EXACT>
@@ -168,8 +175,9 @@ static __device__ __noinline__ FieldSample n_gradient_general(const DevField *fd
 // Default evaluator: closed-form uniform basis, one interval computation per physical axis, no knot
 // comparisons (a fraction 1e-13 outside [0,1) evaluates the neighbouring polynomial piece of a C2 /
 // C0 spline: error << 1e-13).  Falls back to the general routine near the grid ends.
-__device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevField *fd, double x, double y,
-                                                double &n, double &gx, double &gy)
+// Returns true when the position's cell lies inside `in` (then it is also strictly inside the box).
+__device__ __forceinline__ bool n_gradient_cells(const DevField &f, const DevField *fd, const CellBox &in, double x,
+                                                 double y, double &n, double &gx, double &gy)
 {
     // Interval index and cell fraction without conversion instructions or knot loads: vh = (interval
     // coordinate) - 0.5; adding 1.5*2^52 rounds it to the nearest integer = floor(coordinate), which then sits in
@@ -182,10 +190,13 @@ __device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevFiel
     const int lu = __double2loint(mu), lv = __double2loint(mv);
     // |coordinate| < 2^31 <=> high word of the sum is 0x43380000 (or 0x4337ffff for negatives); NaN fails too
     const bool sane = (unsigned)(__double2hiint(mu) - 0x4337ffff) <= 1u && (unsigned)(__double2hiint(mv) - 0x4337ffff) <= 1u;
-    if (!f.fast_ok || !sane || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
-        const FieldSample r = n_gradient_general(fd, x, y);
-        n = r.n; gx = r.gx; gy = r.gy;
-        return;
+    const bool inner = sane && lu >= in.lo_u && lu <= in.hi_u && lv >= in.lo_v && lv <= in.hi_v;
+    if (!inner) { // rare: near the box / grid edge, or arbitrary knots
+        if (!f.fast_ok || !sane || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
+            const FieldSample r = n_gradient_general(fd, x, y);
+            n = r.n; gx = r.gx; gy = r.gy;
+            return false;
+        }
     }
     const double su = (vu - (mu - MAGIC)) + 0.5;
     const double sv = (vv - (mv - MAGIC)) + 0.5;
@@ -214,6 +225,15 @@ __device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevFiel
     }
     gy = au;
     gx = av;
+    return inner;
+}
+
+// Same evaluator without a box (ray start, rtb_field_eval).
+__device__ __forceinline__ void n_gradient_fast(const DevField &f, const DevField *fd, double x, double y,
+                                                double &n, double &gx, double &gy)
+{
+    const CellBox in = {f.flo_u, f.fast_ok ? f.fhi_u : f.flo_u - 1, f.flo_v, f.fhi_v};
+    n_gradient_cells(f, fd, in, x, y, n, gx, gy);
 }
 
 } // namespace rtb

@@ -280,6 +280,7 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     a.tail_zero = (p->flags & RTB_F_NO_TAIL_ZERO) ? 0 : 1;
     a.step = p->step; a.gamma = p->gamma;
     a.limx_i = p->limx_i; a.limx_s = p->limx_s; a.limy_i = p->limy_i; a.limy_s = p->limy_s;
+    a.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
     a.s_ray = sg.out(s_ray, (size_t)rows * 6 * R);
     a.d_ray = sg.out(d_ray, (size_t)3 * R);
     a.last_row = sg.out(last_row, (size_t)6 * R);

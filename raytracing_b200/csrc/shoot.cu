@@ -34,6 +34,7 @@ int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n
     a.R = n; a.max_size = (int)max_size; a.out_stride = 1; a.tail_zero = 0;
     a.step = p->step; a.gamma = p->gamma;
     a.limx_i = p->limx_i; a.limx_s = p->limx_s; a.limy_i = p->limy_i; a.limy_s = p->limy_s;
+    a.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
     a.d_ray = b.d_ray;
     a.exit_out = b.exit_out;
     a.total_steps = ctx->d_total;

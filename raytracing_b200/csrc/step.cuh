@@ -19,6 +19,7 @@ struct RayState {
     double n, gx, gy;   // field at (x,y)
     double coef;        // anisotropy(ang, gamma)
     double inv_n;       // 1/n (default kernels only)
+    double hn;          // h/n (default kernels only): h*(u x grad n)/n and h^2/(2n) share it
 };
 
 // Position advancer of each method: 1 = first_order_taylor, 2 = second_order_taylor, 3 = curvature_t

@@ -61,8 +61,9 @@ struct CostAnisoFast {
 // One step.  Updates the state in place; returns dist = |r1 - r0|.  LAZY: theta of atan2-type
 // updaters is not evaluated (s.ang stale); `i` is the step index (resync schedule).
 template <int METHOD, bool ISO, bool LAZY>
-__device__ __forceinline__ double step_fast(const DevField &f, const DevField *fd, FastState &s, double h, double gamma, double g2m1,
-                                            double (&hist)[3][2], int i, bool bootstrap)
+__device__ __forceinline__ double step_fast(const DevField &f, const DevField *fd, const CellBox &in, FastState &s, double h,
+                                            double gamma, double g2m1, double (&hist)[3][2], int i, bool bootstrap,
+                                            bool &inner)
 {
     constexpr int ADV = advancer_of(METHOD);
     constexpr int UPD = updater_of(METHOD);
@@ -74,7 +75,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         fx = fma(s.ux, h, s.x);
         fy = fma(s.uy, h, s.y);
     } else if (ADV == 2 || bootstrap) {
-        const double q = 0.5 * h * h * s.inv_n;
+        const double q = 0.5 * h * s.hn;
         fx = fma(qx, q, fma(s.ux, h, s.x));
         fy = fma(qy, q, fma(s.uy, h, s.y));
     } else {
@@ -107,8 +108,9 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         }
     }
     double fn, fgx, fgy;
-    n_gradient_fast(f, fd, fx, fy, fn, fgx, fgy);
-    const double inv_fn = rcp_fast(fn);
+    inner = n_gradient_cells(f, fd, in, fx, fy, fn, fgx, fgy); // true: new position strictly inside the box
+    const double inv_fn = rcp_fast3(fn);
+    const double hn1 = h * inv_fn;
 
     const double dx = s.x - fx, dy = s.y - fy;
     const double dist = sqrt_pos(fma(dx, dx, dy * dy));
@@ -143,23 +145,23 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         s.ux = a * r; s.uy = b * r;
         s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux);
     } else if (UPD == 2) { // tfinal_2o RT:374-391
-        // Straight-line form: both rotations use the fixed mid-degree polynomial (valid for |k| < 2^-6, every
+        // Straight-line form: both rotations use the fixed mid-degree polynomial (valid for |k| < 2^-8, every
         // per-step increment in practice) so the whole update is one basic block the scheduler can interleave
         // with the reciprocal / square-root chains; the rare cases (large curvature*step) and the periodic exact
         // resync of (sin, cos) with the accumulated angle are repaired in ONE conditional block afterwards.
-        const double k1 = h * (s.ux * s.gy - s.uy * s.gx) * s.inv_n;
+        const double k1 = (s.ux * s.gy - s.uy * s.gx) * s.hn;
         double s1, c1;
-        rotate_mid(s.uy, s.ux, k1, s1, c1);
-        double k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
+        rotate_small(s.uy, s.ux, k1, s1, c1);
+        double k2 = (c1 * fgy - s1 * fgx) * hn1;
         double ang = s.ang + 0.5 * (k1 + k2);
         double nuy, nux;
         // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
-        rotate_mid(s1, c1, 0.5 * (k2 - k1), nuy, nux);
-        const bool small = abs_lt_hi(k1, HI_2M6) && abs_lt_hi(k2, HI_2M6);
+        rotate_small(s1, c1, 0.5 * (k2 - k1), nuy, nux);
+        const bool small = abs_lt_hi(k1, HI_2M8) && abs_lt_hi(k2, HI_2M8);
         if (!small || (i & RTB_RESYNC_MASK) == 0) {
             if (!small) {
                 sincos_cw(s.ang + k1, s1, c1);
-                k2 = h * (c1 * fgy - s1 * fgx) * inv_fn;
+                k2 = (c1 * fgy - s1 * fgx) * hn1;
                 ang = s.ang + 0.5 * (k1 + k2);
             }
             sincos_cw(ang, nuy, nux);
@@ -183,7 +185,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         s.ang = golden(cf, s.ang - RTB_DELTA_G, s.ang + RTB_DELTA_G);
         sincos_cw(s.ang, s.uy, s.ux);
     }
-    s.x = fx; s.y = fy; s.n = fn; s.inv_n = inv_fn; s.gx = fgx; s.gy = fgy;
+    s.x = fx; s.y = fy; s.n = fn; s.inv_n = inv_fn; s.hn = hn1; s.gx = fgx; s.gy = fgy;
     if (!ISO) {
         const double gs = gamma * s.uy;
         s.coef = sqrt_fast(fma(gs, gs, s.ux * s.ux));

@@ -17,6 +17,7 @@ namespace rtb {
 struct TraceArgs {
     DevField f;
     const DevField *f_dev;     // the same struct in global memory (rare out-of-line paths)
+    CellBox in;                // cells of the fast region strictly inside the box (make_cell_box)
     const double *theta0, *x0, *y0;
     const double *steps;       // per-ray step or nullptr
     const int64_t *max_sizes;  // per-ray max_size or nullptr
@@ -80,6 +81,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
     if (EXACT) n_gradient<true>(a.f, s.x, s.y, s.n, s.gx, s.gy);
     else n_gradient_fast(a.f, a.f_dev, s.x, s.y, s.n, s.gx, s.gy);
     s.inv_n = EXACT ? 0.0 : rcp_fast(s.n);
+    s.hn = h * s.inv_n;
     s.coef = ISO ? 1.0 : anisotropy_sc(s.uy, s.ux, gamma);
     double px, py;
     moments_sc<ISO>(s.n, s.coef, g2m1, s.ux, s.uy, px, py);
@@ -117,6 +119,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
         if (!__any_sync(0xffffffffu, alive)) break;
         if (alive) {
             double dist;
+            bool inner = false; // new position known to be strictly inside the box (no FP64 compares needed)
             if (EXTRA) { pvx = s.x; pvy = s.y; pvT = T; }
             if (EXACT) {
                 double fx, fy, fang, fn, fgx, fgy;
@@ -147,7 +150,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
                 s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             } else {
-                dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3);
+                dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, a.in, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3, inner);
                 if (TRAJ || EXTRA) moments_fast<ISO>(s, g2m1, px, py); // else only the last row's, after the loop
             }
             dist_sim += dist;
@@ -169,7 +172,7 @@ __global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
             }
             // boundary test RT:878 (strict)
-            const bool outside = s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i;
+            const bool outside = !inner && (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i);
             if (outside) {
                 if (EXTRA) { // fraction of the last segment inside the box (first limit crossed)
                     double t = 1.0;
