@@ -53,6 +53,33 @@ __global__ void op_mix(double *out, int iters, double a, double b)
     if (s == 12345.678) out[0] = s;
 }
 
+// Operand-source variants (register-file read bandwidth hypothesis): ILP independent chains per warp with
+//  SRC 0: v = fma(v, a, b), a and b the same registers for every chain (operand reuse cache can serve them)
+//  SRC 1: v = fma(v, c[A], c[B]) with constant-bank operands (no register read for them)
+//  SRC 2: v_k = fma(v_k, a_k, b_k) with distinct registers per chain (three fresh 64-bit register reads each)
+__constant__ double kc[2] = {0.999999, 1e-9};
+template <int ILP, int SRC>
+__global__ void dfma_src(double *out, int iters, double a, double b)
+{
+    double v[ILP], aa[ILP], bb[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) { v[k] = threadIdx.x + k; aa[k] = a + 1e-9 * (k + threadIdx.x); bb[k] = b * (k + 1 + threadIdx.x); }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+#pragma unroll
+            for (int k = 0; k < ILP; ++k) {
+                if (SRC == 0) v[k] = fma(v[k], a, b);
+                if (SRC == 1) v[k] = fma(v[k], kc[0], kc[1]);
+                if (SRC == 2) v[k] = fma(v[k], aa[k], bb[k]);
+            }
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += v[k];
+    if (s == 12345.678) out[0] = s;
+}
+
 template <class F> static float time_ms(F launch)
 {
     cudaEvent_t e0, e1;
@@ -96,6 +123,28 @@ int main()
         ms[3] = time_ms([&] { dfma_chain<4><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
         for (int k = 0; k < 4; ++k) printf("  %.3f", (double)iters * 16 * (k + 1) * w / (ms[k] * 1e-3 * clk));
         printf("\n");
+    }
+    // (2b) operand sources, 5 warps/SMSP (the trace kernel's occupancy)
+    {
+        const int w = 5;
+        const char *nm[3] = {"shared a,b registers", "constant-bank a,b", "distinct a_k,b_k registers"};
+        float ms[3][3];
+        ms[0][0] = time_ms([&] { dfma_src<1, 0><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[0][1] = time_ms([&] { dfma_src<2, 0><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[0][2] = time_ms([&] { dfma_src<4, 0><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[1][0] = time_ms([&] { dfma_src<1, 1><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[1][1] = time_ms([&] { dfma_src<2, 1><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[1][2] = time_ms([&] { dfma_src<4, 1><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[2][0] = time_ms([&] { dfma_src<1, 2><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[2][1] = time_ms([&] { dfma_src<2, 2><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        ms[2][2] = time_ms([&] { dfma_src<4, 2><<<sms, 128 * w>>>(d, iters, 0.999999, 1e-9); });
+        printf("DFMA rate per SMSP by operand source at 5 warps/SMSP (ILP 1, 2, 4):\n");
+        const int il[3] = {1, 2, 4};
+        for (int r = 0; r < 3; ++r) {
+            printf("  %-28s", nm[r]);
+            for (int k = 0; k < 3; ++k) printf("  %.3f", (double)iters * 16 * il[k] * w / (ms[r][k] * 1e-3 * clk));
+            printf("\n");
+        }
     }
     // (3)/(4) op mix at 4 warps/SMSP x ILP 4 (saturating): cycles per warp-instruction group of 4
     const char *names[8] = {"DFMA", "DMUL", "DADD", "DSETP+int add", "F2I.F64 + int add", "MUFU.RCP64H", "DFMA + 1 int op", "DFMA + 2 int ops"};
