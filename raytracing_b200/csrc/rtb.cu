@@ -2,6 +2,7 @@
 // staging, kernel dispatch, Snell metric, FP64 peak probe.  No CPU fallback anywhere: every
 // entry point needs a CUDA device and reports failures through the return code.
 #include "ctx.cuh"
+#include "cell_tables.cuh"
 
 extern "C" int rtb_abi_version(void) { return RTB_ABI_VERSION; }
 
@@ -155,6 +156,24 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
     };
     f.fast_ok = shared_axis(z->tu, z->nu, f.zu, gu->tu, f.gu_, f.flo_u, f.fhi_u) &&
                 shared_axis(z->tv, z->nv, f.zv, gu->tv, f.gv_, f.flo_v, f.fhi_v);
+    // per-cell polynomial tables of the fast region (cell_tables.cuh); without them the general evaluator is used
+    f.pg = nullptr; f.pn = nullptr; f.pstride = 0;
+    if (f.fast_ok) {
+        const size_t ncell = (size_t)(f.fhi_u - f.flo_u + 1) * (size_t)(f.fhi_v - f.flo_v + 1);
+        double2 *pg = nullptr;
+        double *pn = nullptr;
+        if (cudaMalloc(&pg, ncell * 16 * sizeof(double2)) == cudaSuccess) ctx->field_allocs.push_back(pg);
+        if (pg && cudaMalloc(&pn, ncell * 4 * sizeof(double)) == cudaSuccess) ctx->field_allocs.push_back(pn);
+        if (pg && pn) {
+            f.pg = pg; f.pn = pn; f.pstride = f.fhi_v - f.flo_v + 1;
+            cell_table_kernel<<<(unsigned)((ncell + 127) / 128), 128, 0, ctx->stream>>>(f, pg, pn);
+            CK(cudaGetLastError());
+            CK(cudaStreamSynchronize(ctx->stream));
+        } else {
+            (void)cudaGetLastError(); // out of memory for the tables: correct but slow general path
+            f.fast_ok = 0;
+        }
+    }
     ctx->f = f;
     CK(cudaMalloc(&ctx->f_dev, sizeof(DevField)));
     ctx->field_allocs.push_back(ctx->f_dev);
