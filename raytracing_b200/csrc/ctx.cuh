@@ -33,7 +33,7 @@ struct rtb_ctx {
     DevField *f_dev = nullptr;
     std::vector<void *> field_allocs;
     unsigned long long *d_total = nullptr;
-    int block = 128;
+    int block = RTB_BLOCK;
     std::string err;
     // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
     struct PoolBuf { void *p; size_t bytes; bool used; };

@@ -13,6 +13,9 @@ namespace rtb {
 #ifndef RTB_MIN_BLOCKS
 #define RTB_MIN_BLOCKS 5 // default kernels: <= 96 registers -> 5 blocks of 128 threads per SM
 #endif
+#ifndef RTB_BLOCK
+#define RTB_BLOCK 128
+#endif
 
 struct TraceArgs {
     DevField f;
@@ -54,7 +57,7 @@ __device__ __forceinline__ void store_row(double *p, int64_t R, double x, double
 // EXTRA = p_x statistics and/or Snell row capture requested (kept out of the plain kernels: their
 // accumulators cost 15 registers).
 template <int METHOD, bool ISO, bool TRAJ, bool EXACT, bool EXTRA>
-__global__ void __launch_bounds__(128, EXACT ? 4 : RTB_MIN_BLOCKS) trace_kernel(const TraceArgs a)
+__global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB_MIN_BLOCKS) trace_kernel(const TraceArgs a)
 {
     constexpr int UPD = updater_of(METHOD);
     constexpr bool LAZY = !EXACT && !TRAJ && (UPD == 1 || UPD == 3); // theta evaluated once at the end
