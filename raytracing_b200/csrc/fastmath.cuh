@@ -180,9 +180,10 @@ static __device__ __noinline__ double2 sincos_libdevice(double x)
 
 // sin and cos for |x| up to ~1e5 (ray angles are O(1..100)): Cody-Waite reduction by pi/2 with a
 // 3-term split of pi/2, no slow path.  Larger arguments fall back to libdevice.
-__device__ __forceinline__ void sincos_cw(double x, double &s, double &c)
+template <bool FALLBACK>
+__device__ __forceinline__ void sincos_cw_t(double x, double &s, double &c)
 {
-    if (fabs(x) > 1.0e5) { const double2 r = sincos_libdevice(x); s = r.x; c = r.y; return; }
+    if (FALLBACK && fabs(x) > 1.0e5) { const double2 r = sincos_libdevice(x); s = r.x; c = r.y; return; }
     const double q = rint(x * kPio2[0]); // x * 2/pi
     double r = fma(q, kPio2[1], x);      // pi/2 hi (33 bits)
     r = fma(q, kPio2[2], r);             // pi/2 mid
@@ -196,5 +197,8 @@ __device__ __forceinline__ void sincos_cw(double x, double &s, double &c)
     s = (n & 2) ? -ss : ss;
     c = ((n + 1) & 2) ? -cc : cc;
 }
+__device__ __forceinline__ void sincos_cw(double x, double &s, double &c) { sincos_cw_t<true>(x, s, c); }
+// Straight-line variant (no out-of-line call): for |x| > 1e5 the 3-term reduction loses accuracy gradually.
+__device__ __forceinline__ void sincos_cw_inline(double x, double &s, double &c) { sincos_cw_t<false>(x, s, c); }
 
 } // namespace rtb

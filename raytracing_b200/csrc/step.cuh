@@ -67,6 +67,10 @@ struct CostIso { // lambda RT_bench.py:595,697
     {
         double s, c;
         sincos(th, &s, &c);
+        return eval_sc(s, c);
+    }
+    __device__ __forceinline__ double eval_sc(double s, double c) const // reference evaluation order
+    {
         const double a = n1 * c - n0ux - ix;
         const double b = n1 * s - n0uy - iy;
         return a * a + b * b;
@@ -79,6 +83,10 @@ struct CostAniso { // lambda RT_bench.py:728,761
     {
         double s, c;
         sincos(th, &s, &c);
+        return eval_sc(s, c);
+    }
+    __device__ __forceinline__ double eval_sc(double s, double c) const // reference evaluation order
+    {
         const double coef = anisotropy_sc(s, c, gamma);
         const double a = moment_c(n1, coef, g2m1, c, -(s * s)) - mi_x - step * (cgx0 + coef * gx1) / 2.0;
         const double b = moment_c(n1, coef, g2m1, s, c * c) - mi_y - step * (cgy0 + coef * gy1) / 2.0;

@@ -11,12 +11,16 @@
 // tests/test_gpu_trace.py) except where the reference itself is noise-dominated.
 #pragma once
 #include "fastmath.cuh"
+#include "golden_table.cuh"
 #include "step.cuh"
 
 namespace rtb {
 
 typedef RayState FastState; // ang is stale (lazy) for theta_cost_t / finite_diff methods when LAZY
 
+#ifndef RTB_TIE_EPS
+#define RTB_TIE_EPS 3.6e-15 // near-tie band of the golden comparisons (see golden_trig)
+#endif
 #define RTB_RESYNC_MASK 15 // exact sincos every 16 steps bounds the drift of the rotated (sin, cos)
 
 // cos(k) - 1 for |k| <= RTB_SMALL_ANGLE_MAX without cancellation
@@ -31,12 +35,11 @@ __device__ __forceinline__ double cosm1_small(double k2)
     return fma(k2 * k2, p, -0.5 * k2);
 }
 
+// Cost functions of the golden-section angle search (RT:595,697 and RT:728,761) taking (sin, cos) of the probe.
 struct CostIsoFast {
     double n1, ax, ay; // ax = n0*ux + impulse_x
-    __device__ __forceinline__ double operator()(double th) const
+    __device__ __forceinline__ double operator()(double s, double c) const
     {
-        double s, c;
-        sincos_cw(th, s, c);
         const double a = fma(n1, c, -ax), b = fma(n1, s, -ay);
         return fma(a, a, b * b);
     }
@@ -44,19 +47,92 @@ struct CostIsoFast {
 
 struct CostAnisoFast {
     double n1, gamma, g2m1, mx, my, gx1h, gy1h; // mx = mi_x + h*coef_i*gx0/2 ; gx1h = h*gx1/2
-    __device__ __forceinline__ double operator()(double th) const
+    __device__ __forceinline__ double operator()(double s, double c) const
     {
-        double s, c;
-        sincos_cw(th, s, c);
-        const double gs = gamma * s;
-        const double v = fma(gs, gs, c * c);
-        const double coef = sqrt_fast(v), iv = rcp_fast(v);
-        const double nc = n1 * coef, k = g2m1 * iv;
-        const double a = nc * c * fma(-(s * s), k, 1.0) - mx - coef * gx1h;
-        const double b = nc * s * fma(c * c, k, 1.0) - my - coef * gy1h;
+        const double gs = gamma * s, s2 = s * s, c2 = c * c;
+        const double v = fma(gs, gs, c2); // anisotropy^2, in [1, gamma^2]
+        double y;                         // 1/sqrt(v): MUFU seed + one cubically convergent step
+        asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
+        const double e = fma(-v * y, y, 1.0);
+        y = fma(y, fma(e, 0.375, 0.5) * e, y);
+        const double coef = v * y, k = g2m1 * (y * y);
+        const double nc = n1 * coef;
+        const double a = fma(nc * c, fma(-s2, k, 1.0), -fma(coef, gx1h, mx));
+        const double b = fma(nc * s, fma(c2, k, 1.0), -fma(coef, gy1h, my));
         return fma(a, a, b * b);
     }
 };
+
+// golden (RT:175-199) with the trigonometry of the probes done by angle addition.
+//
+// The bracket, the probe angles c, d and every comparison are computed exactly as the reference does (same
+// floating-point expressions, same `while abs(c-d) > tol`, same `if f(c) < f(d)`, result (a+b)/2).  What changes is
+// how sin/cos of a probe is obtained: every call starts from [theta - pi/2, theta + pi/2], so the probe created in
+// iteration k sits at the kept probe -+ pi*rho^(k+4) -- constants (golden_table.cuh) -- plus the rounding of the
+// reference's own expressions, which is measured (eps) and applied to first order.  sin/cos(theta) come from the ray
+// state.  The kept probe keeps its cost value (the reference re-evaluates it at an angle that differs by rounding
+// only: the costs are sums of squares of small residuals, so a change of ~1e-16 in the angle moves them by ~1e-20,
+// far below the ~1e-16 differences the comparisons decide on).  One cost evaluation and ~20 FP64 instructions per
+// iteration instead of two evaluations with a full sincos each.
+// Near-ties -- |f(c) - f(d)| within ~16 ulp-level perturbations of the residuals, i.e. (f(c)-f(d))^2 <=
+// (3.6e-15 * scale)^2 * max f with f = |residual|^2 and scale = the size of the terms the residual is the
+// difference of -- are where the rounding of *any* evaluation decides (among them the exact tie of a ray running
+// along grad n).  They are re-decided with both probes evaluated afresh at the reference's probe angles with a
+// full-accuracy sincos (no cached value, no angle-addition chain); a few per cent of the last iterations.
+// Returns (a+b)/2 and its sin/cos.
+template <class F, class FX>
+__device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_less, double scale, double theta, double st,
+                                              double ct, double &s_out, double &c_out)
+{
+    const double tie2 = (RTB_TIE_EPS * scale) * (RTB_TIE_EPS * scale);
+    double a = theta - RTB_DELTA_G, b = theta + RTB_DELTA_G;
+    double c = b - (b - a) * RTB_GOLD_RATIO;
+    double d = a + (b - a) * RTB_GOLD_RATIO;
+    const double S0 = kGolden0[0], C0 = kGolden0[1], P0 = kGolden0[2];
+    // left probe c = theta - P0 + rounding, right probe d = theta + P0 + rounding
+    double Lpsi = c - theta, Rpsi = d - theta;
+    double Ls = fma(-ct, S0, st * C0), Lc = fma(st, S0, ct * C0);
+    double Rs = fma(ct, S0, st * C0), Rc = fma(-st, S0, ct * C0);
+    {
+        const double el = Lpsi + P0, er = Rpsi - P0;
+        const double t0 = fma(Lc, el, Ls), t1 = fma(Rc, er, Rs);
+        Lc = fma(-Ls, el, Lc); Rc = fma(-Rs, er, Rc);
+        Ls = t0; Rs = t1;
+    }
+    double Lf = cost(Ls, Lc), Rf = cost(Rs, Rc);
+    int k = 0;
+#pragma unroll 1
+    while (fabs(c - d) > RTB_GOLD_TOL) {
+        bool left = Lf < Rf; // RT:189: if func(c) < func(d): b = d  else: a = c
+        const double df = Lf - Rf;
+        if (df * df <= tie2 * fmax(Lf, Rf)) left = exact_less(c, d);
+        const double Ws = left ? Ls : Rs, Wc = left ? Lc : Rc, Wpsi = left ? Lpsi : Rpsi; // kept probe
+        b = left ? d : b;
+        a = left ? a : c;
+        c = b - (b - a) * RTB_GOLD_RATIO;
+        d = a + (b - a) * RTB_GOLD_RATIO;
+        const int kk = min(k, RTB_GOLDEN_ROT_N - 1);
+        const double2 r = kGoldenRot[kk];
+        const double sgn = left ? -1.0 : 1.0; // the new probe lies left of the kept one when b moved
+        const double psi = (left ? c : d) - theta;
+        const double sr = sgn * r.x;
+        const double ns = fma(Wc, sr, Ws * r.y), nc = fma(-Ws, sr, Wc * r.y);
+        const double eps = psi - fma(sgn, kGoldenDelta[kk], Wpsi);
+        const double fs = fma(nc, eps, ns), fc = fma(-ns, eps, nc);
+        const double ff = cost(fs, fc);
+        // left: (L, R) <- (new, old L);  else: (L, R) <- (old R, new)
+        const double oLs = Ls, oLc = Lc, oLpsi = Lpsi, oLf = Lf;
+        Ls = left ? fs : Rs; Lc = left ? fc : Rc; Lpsi = left ? psi : Rpsi; Lf = left ? ff : Rf;
+        Rs = left ? oLs : fs; Rc = left ? oLc : fc; Rpsi = left ? oLpsi : psi; Rf = left ? oLf : ff;
+        ++k;
+    }
+    const double th = (b + a) / 2.0;
+    // sin/cos of the result from the left probe (|offset| <= final bracket ~3e-8: second order is exact to 1e-23)
+    const double e = (th - theta) - Lpsi, e2h = 0.5 * e * e;
+    s_out = fma(-Ls, e2h, fma(Lc, e, Ls));
+    c_out = fma(-Lc, e2h, fma(-Ls, e, Lc));
+    return th;
+}
 
 // One step.  Updates the state in place; returns dist = |r1 - r0|.  LAZY: theta of atan2-type
 // updaters is not evaluated (s.ang stale); `i` is the step index (resync schedule).
@@ -172,8 +248,16 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         cf.n1 = fn;
         cf.ax = fma(0.5 * h, s.gx + fgx, s.n * s.ux);
         cf.ay = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
-        s.ang = golden(cf, s.ang - RTB_DELTA_G, s.ang + RTB_DELTA_G);
-        sincos_cw(s.ang, s.uy, s.ux);
+        auto exact_less = [&](double pc, double pd) { // near-ties: both probes re-evaluated with a full sincos
+            double s1, c1, s2, c2;
+            sincos_cw_inline(pc, s1, c1);
+            sincos_cw_inline(pd, s2, c2);
+            return cf(s1, c1) < cf(s2, c2);
+        };
+        double ns, nc;
+        s.ang = golden_trig(cf, exact_less, fn, s.ang, s.uy, s.ux, ns, nc);
+        if ((i & RTB_RESYNC_MASK) == 0) sincos_cw(s.ang, ns, nc); // periodic exact resync of the carried (sin, cos)
+        s.uy = ns; s.ux = nc;
     } else { // golden, anisotropic cost RT:728,761
         CostAnisoFast cf;
         cf.n1 = fn; cf.gamma = gamma; cf.g2m1 = g2m1;
@@ -182,8 +266,16 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         cf.mx = fma(0.5 * h * s.coef, s.gx, nc * s.ux * fma(-(s.uy * s.uy), g2m1 * ic2, 1.0));
         cf.my = fma(0.5 * h * s.coef, s.gy, nc * s.uy * fma(s.ux * s.ux, g2m1 * ic2, 1.0));
         cf.gx1h = 0.5 * h * fgx; cf.gy1h = 0.5 * h * fgy;
-        s.ang = golden(cf, s.ang - RTB_DELTA_G, s.ang + RTB_DELTA_G);
-        sincos_cw(s.ang, s.uy, s.ux);
+        auto exact_less = [&](double pc, double pd) { // near-ties: both probes re-evaluated with a full sincos
+            double s1, c1, s2, c2;
+            sincos_cw_inline(pc, s1, c1);
+            sincos_cw_inline(pd, s2, c2);
+            return cf(s1, c1) < cf(s2, c2);
+        };
+        double nsin, ncos;
+        s.ang = golden_trig(cf, exact_less, fn * fmax(gamma, 1.0), s.ang, s.uy, s.ux, nsin, ncos);
+        if ((i & RTB_RESYNC_MASK) == 0) sincos_cw(s.ang, nsin, ncos);
+        s.uy = nsin; s.ux = ncos;
     }
     s.x = fx; s.y = fy; s.n = fn; s.inv_n = inv_fn; s.hn = hn1; s.gx = fgx; s.gy = fgy;
     if (!ISO) {
