@@ -26,6 +26,13 @@ sys.path.insert(0, ROOT)
 SCENARIO = "2"
 METHOD = 6
 RAYS_PER_GPU = 1 << 20
+# Executed (not algorithmic) FP64 work of the op6 FINAL kernel per ray-step, counted by ncu on this workload
+# (profiles/r1f_ncu_full_op6_fisheye1M.csv + the per-instruction page): 64.1 DFMA + 24.3 DMUL + 17.3 DADD warp
+# instructions per warp-step.  The algorithmic figure of SURVEY.md 8(d) (376 flop: B-spline-form field evaluation,
+# 25 flop per sin or cos) is larger than what the kernel executes, so `roofline.frac` can exceed 1; the executed
+# figures below are the hardware-side view of the same launch.
+NCU_OP6 = {"dfma": 64.1, "dmul": 24.3, "dadd": 17.3, "l1_data_pipe_frac": 0.84, "fp64_pipe_active_frac": 0.606,
+           "source": "profiles/r1f_ncu_full_op6_fisheye1M.csv"}
 METRIC = "fp64_ray_steps_per_s"
 UNIT = "ray-steps/s"
 
@@ -256,6 +263,13 @@ def run_cuda(args):
                              "frac": achieved / (fp64_peak / 1e12), "traffic": None,
                              "kernel": "trace_kernel<6,iso,final>", "kernel_ms": k_ms,
                              "flop_per_ray_step": K.F_ALG[METHOD],
+                             "executed": {"fp64_inst_per_ray_step": NCU_OP6["dfma"] + NCU_OP6["dmul"] + NCU_OP6["dadd"],
+                                          "flop_per_ray_step": 2 * NCU_OP6["dfma"] + NCU_OP6["dmul"] + NCU_OP6["dadd"],
+                                          "tflops": per_gpu_steps * (2 * NCU_OP6["dfma"] + NCU_OP6["dmul"] + NCU_OP6["dadd"])
+                                          / (k_ms * 1e-3) / 1e12,
+                                          "ncu_fp64_pipe_active_frac": NCU_OP6["fp64_pipe_active_frac"],
+                                          "ncu_l1_data_pipe_frac": NCU_OP6["l1_data_pipe_frac"],
+                                          "source": NCU_OP6["source"]},
                              "peak_source": "measured live: rtb_fp64_peak (DFMA stream on all SMs); "
                                             "MEASURED_PEAKS.json has no FP64 figure"},
                 "e2e": {"value": e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
