@@ -60,9 +60,10 @@ typedef struct {
 
 /* rtb_params.flags */
 #define RTB_F_INTERFACE 1u   /* op_interface: compute the Snell error metric (RT:896-919) into `errors` */
-#define RTB_F_EXACT_BASIS 2u /* evaluate B-spline bases by FITPACK's Cox-de Boor recurrence with the
-                                real knots everywhere (default: closed-form uniform-knot basis where the
-                                knots are uniform, recurrence elsewhere; differs by < 1e-13) */
+#define RTB_F_EXACT_BASIS 2u /* faithful kernels: FITPACK's Cox-de Boor recurrence with the real knots, libm-grade
+                                sin/cos/atan2, IEEE division and sqrt, the reference's evaluation order.
+                                Default: per-cell expanded polynomials on the uniform part of the grid and the
+                                re-associated step arithmetic of step_fast.cuh; results differ by < 1e-12 */
 #define RTB_F_NO_TAIL_ZERO 4u /* s_ray was zero-filled by the caller: do not write the rows after a ray's
                                  last step (np.zeros, RT:802) */
 
@@ -176,6 +177,17 @@ int rtb_shoot_coarse(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem 
 int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_shoot_problem *q, const double *lo,
                      const double *hi, double *theta, double *result, int64_t *iterations,
                      rtb_stats *stats);
+
+/*
+ * Iso-travel-time ("wavefront") points of a traced fan: the arithmetic of the reference's wavefront plot
+ * (graficar RT:987-1007).  For every ray k and time times[j]: PchipInterpolator(t_ray, x)(tau), ...(y), ...(angle)
+ * over rows 0..d_ray[2,k] of the full s_ray (out_stride 1), for rays with max(t_ray) >= tau.
+ *   out (4, nt, R): x, y, group angle, valid flag (1.0 / 0.0; x = y = angle = 0 where invalid)
+ * The cross-ray part of the plot (sorting the points, PCHIP of x over y and its normals, RT:1009-1024) has at most
+ * ray_count points per time and stays on the host (raytracing_b200.wavefront).
+ */
+int rtb_wavefront(rtb_ctx *ctx, int32_t ptr_kind, const double *s_ray, const double *d_ray, int64_t rows,
+                  int64_t R, const double *times, int32_t nt, double *out);
 
 /*
  * Measured FP64 pipe peak (dependent-free DFMA streams on every SM), the roofline denominator

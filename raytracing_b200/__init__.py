@@ -13,5 +13,6 @@ from .api import (trazar, search_delta, n_gradient, find_delta_s, sweep_candidat
                   remove_outliers_iqr, benchmark_statistic, get_engine)
 from .shooting import (shooting_search, targets_from_angles, sweep_two_point, brackets_from_index,
                        reduce_argmin, candidate_rows, default_source)
+from .wavefront import wavefront_points, wavefront, pchip_knot_derivatives
 
 __all__ = [n for n in dir() if not n.startswith("_")]

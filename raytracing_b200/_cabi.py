@@ -12,7 +12,7 @@ RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -
 
 # every symbol include/rtb.h declares
 EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
-           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine")
+           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront")
 
 
 class RtbSpline(C.Structure):
@@ -80,5 +80,7 @@ def load():
     lib.rtb_shoot_refine.restype = C.c_int
     lib.rtb_shoot_refine.argtypes = [vp, C.POINTER(RtbParams), C.POINTER(RtbShootProblem), vp, vp, vp, vp,
                                      C.POINTER(i64), C.POINTER(RtbStats)]
+    lib.rtb_wavefront.restype = C.c_int
+    lib.rtb_wavefront.argtypes = [vp, i32, vp, vp, i64, i64, vp, i32, vp]
     _lib = lib
     return lib

@@ -97,3 +97,18 @@ def test_field_builder_matches_reference_bytes(golden_field):
     assert z.tck[2].size == 261121 and len(grd[0].tck[0]) == 515
     z, grd = rt.build_field("3")
     assert grd[0].tck[2].size == 397243 and (len(grd[0].tck[0]), len(grd[0].tck[1])) == (543, 741)
+
+
+def test_pchip_knot_derivatives_match_scipy():
+    """Host part of the wavefront product (RT_bench.py:1017-1019): derivative of the PCHIP interpolant at its knots."""
+    from scipy.interpolate import PchipInterpolator
+    import raytracing_b200 as rt
+    rng = np.random.default_rng(3)
+    for n in (2, 3, 4, 9, 31):
+        x = np.sort(rng.uniform(-2, 1, n))
+        y = np.cumsum(rng.normal(0, 1, n))
+        if n == 9:
+            y[4] = y[3]          # flat segment -> zero derivative rule
+        d = rt.pchip_knot_derivatives(x, y)
+        r = PchipInterpolator(x, y).derivative()(x)
+        assert np.abs(d - r).max() <= 1e-13 * max(1.0, np.abs(r).max())
