@@ -149,3 +149,23 @@ def test_wavefront_points_vs_scipy_pchip(engine, uc, m):
             # undo the reference's pairing quirk (angles in ray order, normals in y order) for the physics check
             ang_sorted = mid["angle"][np.searchsorted(np.sort(mid["rays"]), mid["rays"])]
             assert np.abs(ang_sorted[inner] - mid["normal_angles"][inner]).max() < 0.05
+
+
+def test_cli_reproduces_reference_results(capsys):
+    """the non-interactive mirror prints the reference's RESULTS lines with the reference's numbers
+    (BASELINE.md fingerprints of interface op6: mean error 0.033879, total distance 422.3026202499)."""
+    from raytracing_b200 import cli
+    info = cli.run("interface", 6, "default", show=False)
+    out = capsys.readouterr().out
+    assert "RESULTS" in out and "Average ray error: " in out and "Total travelled distance: " in out
+    assert abs(info["metric"] - 0.033879) < 1e-6 and abs(info["total_distance"] - 422.3026202499) < 1e-9
+    info = cli.run("4", 2, "calibrated", show=False)          # anisotropy menu answer 2 = op11, SIGMA/2.74
+    assert info["method"] == 11 and abs(info["DELTA_S"] - rt.SIGMA / 2.74) < 1e-15
+    z, grd = rt.build_field("4")
+    s_ray, d_ray, _t, _e = rt.trazar(11, z, grd, False, rt.SIGMA / 2.74, rt.DELTA_S_DIVISOR_FISHEYE + 1, "4")
+    assert info["total_distance"] == float(np.sum(d_ray[1])) and info["ray_steps"] == int(d_ray[2].sum())
+    assert info["metric"] == float(np.mean([rt.px_cv(s_ray[:, 2, i]) for i in range(1, s_ray.shape[2] - 1)]))
+    info = cli.run("fisheye", 6, "search", show=False)
+    assert "divisor" in info and info["metric"] < 5.0
+    assert cli.main(["--scenario", "3", "--method", "1", "--quiet", "--json"]) == 0
+    assert '"scenario": "3"' in capsys.readouterr().out

@@ -112,3 +112,21 @@ def test_pchip_knot_derivatives_match_scipy():
         d = rt.pchip_knot_derivatives(x, y)
         r = PchipInterpolator(x, y).derivative()(x)
         assert np.abs(d - r).max() <= 1e-13 * max(1.0, np.abs(r).max())
+
+
+def test_cli_menu_mapping_and_results_wording(capsys):
+    from raytracing_b200 import cli
+    assert [cli.menu_to_method("1", k) for k in (1, 6, 9)] == [1, 6, 9]
+    assert cli.menu_to_method("4", 1) == 10 and cli.menu_to_method("4", 2) == 11      # RT:1286-1290
+    for bad in (("4", 3), ("2", 10), ("1", 0)):
+        with pytest.raises(ValueError):
+            cli.menu_to_method(*bad)
+    cli.print_results("2", 1.5)
+    cli.print_results("1", 0.25)
+    cli.print_results("3", 0.01)
+    out = capsys.readouterr().out
+    assert "Closure error  1.5 %" in out and "Average ray error:  0.25 degrees" in out
+    assert "Average ray Coefficient of Variation:  0.01" in out and out.count("RESULTS") == 3
+    s = np.zeros((4, 6, 3)); s[-1, 0, 0] = 1.0
+    assert cli.results_metric("2", s, None) == 0.0
+    assert cli.results_metric("1", None, np.array([0.1, 0.3])) == pytest.approx(0.2)
