@@ -108,6 +108,31 @@ int rtb_abi_version(void);
 int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline *gu, const rtb_spline *gv);
 
 /*
+ * interpolacion (RT:435-464) on the device: from the samples Z (my, mx) of the index field on the grid y[my] x x[mx]
+ * (genZ RT:412-433; Z[i][j] = f(x[j], y[i])) to the same resident field rtb_set_field produces, without scipy:
+ *   GradX, GradY = np.gradient(Z, delta, edge_order=2)                      (RT:449; bit-exact)
+ *   z    = RectBivariateSpline(y, x, Z, kx=1, ky=1)                         (RT:455; coefficients = samples)
+ *   grd  = RectBivariateSpline(y, x, GradX | GradY, kx=3, ky=3)             (RT:456-457; FITPACK s=0 knots,
+ *          coefficients from the same collocation system by banded LU: equal to scipy's to a few ulp of max|Grad|)
+ * `delta` is what the reference feeds np.gradient -- the global DELTA, not the true spacing of linspace (RT:449).
+ * y, x, Z are host or device pointers per ptr_kind.  stats: kernel_ms = gradient + substitution sweeps,
+ * total_ms = whole call including the cell tables.
+ */
+int rtb_fit_field(rtb_ctx *ctx, int32_t ptr_kind, const double *y, int64_t my, const double *x, int64_t mx,
+                  const double *Z, double delta, rtb_stats *stats);
+
+/* np.gradient(Z, delta, edge_order=2) alone (RT:449): g0 = d/d(axis 0), g1 = d/d(axis 1), both (my, mx). */
+int rtb_gradient(rtb_ctx *ctx, int32_t ptr_kind, const double *Z, int64_t my, int64_t mx, double delta,
+                 double *g0, double *g1);
+
+/*
+ * Read the resident field back in scipy's tck form (host pointers): which = 0 (z), 1 (grd[0]), 2 (grd[1]).
+ * Any of nu, nv, tu, tv, c may be NULL; call once with the arrays NULL to learn nu, nv
+ * (c has (nu-k-1)*(nv-k-1) entries, k = 1 for z and 3 for grd).
+ */
+int rtb_get_field(rtb_ctx *ctx, int32_t which, int32_t *nu, int32_t *nv, double *tu, double *tv, double *c);
+
+/*
  * n_gradient (RT:141-156) on `n` points: out_n[i], out_gx[i] = grd[1](y,x), out_gy[i] = grd[0](y,x).
  */
 int rtb_field_eval(rtb_ctx *ctx, int32_t ptr_kind, uint32_t flags, const double *x, const double *y,

@@ -12,7 +12,8 @@ RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -
 
 # every symbol include/rtb.h declares
 EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
-           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront")
+           "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront",
+           "rtb_fit_field", "rtb_gradient", "rtb_get_field")
 
 
 class RtbSpline(C.Structure):
@@ -82,5 +83,11 @@ def load():
                                      C.POINTER(i64), C.POINTER(RtbStats)]
     lib.rtb_wavefront.restype = C.c_int
     lib.rtb_wavefront.argtypes = [vp, i32, vp, vp, i64, i64, vp, i32, vp]
+    lib.rtb_fit_field.restype = C.c_int
+    lib.rtb_fit_field.argtypes = [vp, i32, vp, i64, vp, i64, vp, C.c_double, C.POINTER(RtbStats)]
+    lib.rtb_gradient.restype = C.c_int
+    lib.rtb_gradient.argtypes = [vp, i32, vp, i64, i64, C.c_double, vp, vp]
+    lib.rtb_get_field.restype = C.c_int
+    lib.rtb_get_field.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, vp]
     _lib = lib
     return lib

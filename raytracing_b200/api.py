@@ -18,6 +18,32 @@ def get_engine(device=0):
     return _ENGINES[device]
 
 
+def interpolacion_gpu(x, y, Z, delta=None, engine=None):
+    """interpolacion(x, y, Z) (RT_bench.py:435-464) with np.gradient and the three RectBivariateSpline fits done on
+    the GPU (rtb_fit_field): returns (z, grd) handles every function here accepts in place of the scipy objects.
+    The gradient is bit-exact, the spline coefficients equal scipy's to a few ulp of max|gradient|."""
+    eng = engine or get_engine()
+    return eng.fit_field(x, y, Z, K.DELTA if delta is None else delta)
+
+
+_GPU_FIELDS = {}
+
+
+def build_field_gpu(user_choice, engine=None):
+    """build_field with the fit on the GPU: genZ on the host (the scenario functions are numpy expressions of the
+    reference, RT:201-261), everything after it on the device.  Cached per (engine, scenario function)."""
+    from .field import genZ
+    eng = engine or get_engine()
+    uc = K.scenario_id(user_choice)
+    f = K.SCENARIO_FUNCS[uc]
+    lim = K.constants(uc)[5:9]
+    key = (id(eng), f.__name__, lim)
+    if key not in _GPU_FIELDS:
+        x, y, _X, _Y, Z = genZ(lim[0], lim[1], lim[2], lim[3], f)
+        _GPU_FIELDS[key] = interpolacion_gpu(x, y, Z, engine=eng)
+    return _GPU_FIELDS[key]
+
+
 def n_gradient(vector, grd, z, engine=None):
     """RT_bench.py:141-156: returns (n, array([dn/dx, dn/dy])) at `vector` = (x, y)."""
     eng = engine or get_engine()

@@ -14,7 +14,7 @@ import time
 import numpy as np
 
 from . import constants as K
-from .api import benchmark_statistic, find_delta_s, get_engine, px_cv, trazar
+from .api import benchmark_statistic, build_field_gpu, find_delta_s, get_engine, px_cv, trazar
 from .field import build_field
 
 SCENARIOS = {"interface": "1", "fisheye": "2", "vert_heterogeneous": "3", "anisotropy": "4"}
@@ -66,13 +66,14 @@ def print_results(uc, metric, out=sys.stdout):
         print("Average ray Coefficient of Variation: ", metric, file=out)
 
 
-def run(scenario, method_choice, delta_s="default", benchmark=False, trials=100, show=True, out=sys.stdout, device=0):
+def run(scenario, method_choice, delta_s="default", benchmark=False, trials=100, show=True, out=sys.stdout, device=0,
+        fit="device"):
     """One pass through the reference's main(): returns a dict with everything printed."""
     uc = SCENARIOS.get(str(scenario), str(scenario))
     uc = K.scenario_id(uc)
     m = menu_to_method(uc, method_choice)
     eng = get_engine(device)
-    z, grd = build_field(uc)
+    z, grd = build_field_gpu(uc, eng) if fit == "device" else build_field(uc)    # interpolacion, RT:1588
     step, divisor = K.DELTA_S, K.DELTA_S_DIVISOR_FISHEYE
     info = dict(scenario=uc, method=m, algorithm=MESSAGES[m - 1].strip())
     if delta_s == "search":                                   # RT:1299-1406
@@ -119,8 +120,10 @@ def main(argv=None):
                                                          "the interface scenario (RT:1387, 1470)")
     ap.add_argument("--json", action="store_true", help="also print the results as one JSON line")
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--fit", default="device", choices=["device", "scipy"],
+                    help="where interpolacion() runs: rtb_fit_field on the GPU, or scipy on the host as the reference")
     a = ap.parse_args(argv)
-    info = run(a.scenario, a.method, a.delta_s, a.benchmark, a.trials, not a.quiet, device=a.device)
+    info = run(a.scenario, a.method, a.delta_s, a.benchmark, a.trials, not a.quiet, device=a.device, fit=a.fit)
     if a.json:
         print(json.dumps(info))
     return 0 if "error" not in info else 1

@@ -54,6 +54,12 @@ static inline int fail(rtb_ctx *c, int code, const char *what, cudaError_t e = c
         if (e_ != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, #call, e_);     \
     } while (0)
 
+// Field construction pieces defined in rtb.cu and shared with fit.cu.
+void rtb_free_field(rtb_ctx *ctx);
+int rtb_make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax);
+int rtb_finish_field(rtb_ctx *ctx, DevField &f, const double *tzu, int nzu, const double *tzv, int nzv,
+                     const double *tgu, const double *tgv);
+
 // Cells of the default evaluator's fast region that lie strictly inside the box (two cells of margin cover the
 // half-ulp slop of the device-side index): a position indexed into them needs no FP64 box compares.
 static inline CellBox make_cell_box(const DevField &f, double limx_i, double limx_s, double limy_i, double limy_s)

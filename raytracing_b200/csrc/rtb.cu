@@ -32,7 +32,7 @@ extern "C" int rtb_create(int device, rtb_ctx **out)
     return RTB_OK;
 }
 
-static void free_field(rtb_ctx *ctx)
+void rtb_free_field(rtb_ctx *ctx)
 {
     for (void *p : ctx->field_allocs) cudaFree(p);
     ctx->field_allocs.clear();
@@ -43,7 +43,7 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    free_field(ctx);
+    rtb_free_field(ctx);
     for (auto &b : ctx->pool) cudaFree(b.p);
     if (ctx->d_total) cudaFree(ctx->d_total);
     for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -66,7 +66,7 @@ extern "C" int rtb_set_stream(rtb_ctx *ctx, void *cuda_stream)
 }
 
 // Knot-vector metadata for the device interval guess and the uniform-basis fast path.
-static int make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax)
+int rtb_make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax)
 {
     if (!t || n < 2 * (k + 1)) return fail(ctx, RTB_ERR_ARG, "spline: too few knots");
     for (int i = 0; i + 1 < n; ++i)
@@ -112,37 +112,12 @@ static int make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax)
     return RTB_OK;
 }
 
-extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline *gu, const rtb_spline *gv)
+// Second half of building a field, shared by rtb_set_field and rtb_fit_field (fit.cu): detects the region where one
+// interval / fraction per physical axis serves all three splines, expands the per-cell tables and publishes `f`.
+// tzu/tzv/tgu/tgv are HOST copies of the knots whose device copies the axes of `f` already hold.
+int rtb_finish_field(rtb_ctx *ctx, DevField &f, const double *tzu, int nzu, const double *tzv, int nzv,
+                     const double *tgu, const double *tgv)
 {
-    if (!ctx || !z || !gu || !gv) return fail(ctx, RTB_ERR_ARG, "rtb_set_field: null argument");
-    if (z->ku != 1 || z->kv != 1 || gu->ku != 3 || gu->kv != 3 || gv->ku != 3 || gv->kv != 3)
-        return fail(ctx, RTB_ERR_ARG, "rtb_set_field: expected bilinear z and bicubic grd (RT_bench.py:455-457)");
-    if (gu->nu != gv->nu || gu->nv != gv->nv || std::memcmp(gu->tu, gv->tu, sizeof(double) * gu->nu) ||
-        std::memcmp(gu->tv, gv->tv, sizeof(double) * gu->nv))
-        return fail(ctx, RTB_ERR_ARG, "rtb_set_field: grd[0] and grd[1] must share their knots");
-    CK(cudaSetDevice(ctx->device));
-    free_field(ctx);
-    DevField f;
-    int rc;
-    if ((rc = make_axis(ctx, z->tu, z->nu, 1, &f.zu))) return rc;
-    if ((rc = make_axis(ctx, z->tv, z->nv, 1, &f.zv))) return rc;
-    if ((rc = make_axis(ctx, gu->tu, gu->nu, 3, &f.gu_))) return rc;
-    if ((rc = make_axis(ctx, gu->tv, gu->nv, 3, &f.gv_))) return rc;
-    f.ncz = z->nv - 2;
-    f.ncg = gu->nv - 4;
-    const size_t nz = (size_t)(z->nu - 2) * f.ncz, ng = (size_t)(gu->nu - 4) * f.ncg;
-    double *dz = nullptr;
-    double2 *dg = nullptr;
-    CK(cudaMalloc(&dz, nz * sizeof(double)));
-    ctx->field_allocs.push_back(dz);
-    CK(cudaMalloc(&dg, ng * sizeof(double2)));
-    ctx->field_allocs.push_back(dg);
-    CK(cudaMemcpy(dz, z->c, nz * sizeof(double), cudaMemcpyHostToDevice));
-    std::vector<double2> inter(ng);
-    for (size_t i = 0; i < ng; ++i) inter[i] = make_double2(gu->c[i], gv->c[i]);
-    CK(cudaMemcpy(dg, inter.data(), ng * sizeof(double2), cudaMemcpyHostToDevice));
-    f.cz = dz;
-    f.cg = dg;
     // fast path: bilinear knots == cubic knots shifted by one over the uniform cubic range
     auto shared_axis = [](const double *tz, int nz, const DevAxis &az, const double *tg, const DevAxis &ag, int &lo, int &hi) {
         lo = ag.lo; hi = ag.hi;
@@ -154,8 +129,8 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
             if (tz[l - 1] != tg[l] || tz[l] != tg[l + 1]) return false;
         return true;
     };
-    f.fast_ok = shared_axis(z->tu, z->nu, f.zu, gu->tu, f.gu_, f.flo_u, f.fhi_u) &&
-                shared_axis(z->tv, z->nv, f.zv, gu->tv, f.gv_, f.flo_v, f.fhi_v);
+    f.fast_ok = shared_axis(tzu, nzu, f.zu, tgu, f.gu_, f.flo_u, f.fhi_u) &&
+                shared_axis(tzv, nzv, f.zv, tgv, f.gv_, f.flo_v, f.fhi_v);
     // per-cell polynomial tables of the fast region (cell_tables.cuh); without them the general evaluator is used
     f.pg = nullptr; f.pn = nullptr; f.pstride = 0;
     if (f.fast_ok) {
@@ -180,6 +155,40 @@ extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline
     CK(cudaMemcpy(ctx->f_dev, &f, sizeof(DevField), cudaMemcpyHostToDevice));
     ctx->has_field = true;
     return RTB_OK;
+}
+
+extern "C" int rtb_set_field(rtb_ctx *ctx, const rtb_spline *z, const rtb_spline *gu, const rtb_spline *gv)
+{
+    if (!ctx || !z || !gu || !gv) return fail(ctx, RTB_ERR_ARG, "rtb_set_field: null argument");
+    if (z->ku != 1 || z->kv != 1 || gu->ku != 3 || gu->kv != 3 || gv->ku != 3 || gv->kv != 3)
+        return fail(ctx, RTB_ERR_ARG, "rtb_set_field: expected bilinear z and bicubic grd (RT_bench.py:455-457)");
+    if (gu->nu != gv->nu || gu->nv != gv->nv || std::memcmp(gu->tu, gv->tu, sizeof(double) * gu->nu) ||
+        std::memcmp(gu->tv, gv->tv, sizeof(double) * gu->nv))
+        return fail(ctx, RTB_ERR_ARG, "rtb_set_field: grd[0] and grd[1] must share their knots");
+    CK(cudaSetDevice(ctx->device));
+    rtb_free_field(ctx);
+    DevField f;
+    int rc;
+    if ((rc = rtb_make_axis(ctx, z->tu, z->nu, 1, &f.zu))) return rc;
+    if ((rc = rtb_make_axis(ctx, z->tv, z->nv, 1, &f.zv))) return rc;
+    if ((rc = rtb_make_axis(ctx, gu->tu, gu->nu, 3, &f.gu_))) return rc;
+    if ((rc = rtb_make_axis(ctx, gu->tv, gu->nv, 3, &f.gv_))) return rc;
+    f.ncz = z->nv - 2;
+    f.ncg = gu->nv - 4;
+    const size_t nz = (size_t)(z->nu - 2) * f.ncz, ng = (size_t)(gu->nu - 4) * f.ncg;
+    double *dz = nullptr;
+    double2 *dg = nullptr;
+    CK(cudaMalloc(&dz, nz * sizeof(double)));
+    ctx->field_allocs.push_back(dz);
+    CK(cudaMalloc(&dg, ng * sizeof(double2)));
+    ctx->field_allocs.push_back(dg);
+    CK(cudaMemcpy(dz, z->c, nz * sizeof(double), cudaMemcpyHostToDevice));
+    std::vector<double2> inter(ng);
+    for (size_t i = 0; i < ng; ++i) inter[i] = make_double2(gu->c[i], gv->c[i]);
+    CK(cudaMemcpy(dg, inter.data(), ng * sizeof(double2), cudaMemcpyHostToDevice));
+    f.cz = dz;
+    f.cg = dg;
+    return rtb_finish_field(ctx, f, z->tu, z->nu, z->tv, z->nv, gu->tu, gu->tv);
 }
 
 template <bool EXACT>

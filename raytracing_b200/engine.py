@@ -59,6 +59,24 @@ def _is_torch(x):
     return type(x).__module__.startswith("torch")
 
 
+class DeviceSpline:
+    """One of the three splines of a field fitted on the GPU (Engine.fit_field): stands where the reference passes a
+    scipy RectBivariateSpline (z, grd[0], grd[1] of interpolacion(), RT_bench.py:455-458).  `.tck` / `.degrees` read
+    the coefficients back in scipy's layout; the samples are kept so another engine (another GPU) can refit."""
+
+    def __init__(self, fit, which):
+        self.fit, self.which = fit, which
+        self.degrees = (1, 1) if which == 0 else (3, 3)
+
+    @property
+    def tck(self):
+        if self.which not in self.fit["tck"]:
+            eng = self.fit["engine"]
+            eng._ensure_fit(self.fit)
+            self.fit["tck"][self.which] = eng.get_field(self.which)
+        return self.fit["tck"][self.which]
+
+
 class Engine:
     """One librtb context on one GPU."""
 
@@ -99,6 +117,10 @@ class Engine:
     def set_field(self, z, grd):
         """Upload z (bilinear n) and grd = (dn/dy spline, dn/dx spline) as interpolacion() returns
         them (RT_bench.py:455-458); scipy objects or (tu, tv, c, ku, kv) tuples."""
+        if isinstance(z, DeviceSpline):
+            if not (isinstance(grd[0], DeviceSpline) and grd[0].fit is z.fit and grd[1].fit is z.fit):
+                raise ValueError("set_field: z and grd must come from one fit_field call")
+            return self._ensure_fit(z.fit)
         key = (id(z), id(grd[0]), id(grd[1]))
         if key == self._field_key:
             return
@@ -108,6 +130,61 @@ class Engine:
         self._check(self._lib.rtb_set_field(self._ctx, *[C.byref(s) for s in structs]))
         self._field_key = key
         self._keep = (z, grd)  # keep ids alive so the cache key stays valid
+
+    def _ensure_fit(self, fit):
+        """Make the field of a fit_field result the resident one (refit from the kept samples if it was replaced)."""
+        key = ("fit", id(fit))
+        if key == self._field_key:
+            return
+        x, y, Z = fit["x"], fit["y"], fit["Z"]
+        stats = _cabi.RtbStats()
+        if _is_torch(Z):
+            kind, ptrs = _cabi.RTB_PTR_DEVICE, (y.data_ptr(), x.data_ptr(), Z.data_ptr())
+        else:
+            kind, ptrs = _cabi.RTB_PTR_HOST, (y.ctypes.data, x.ctypes.data, Z.ctypes.data)
+        self._check(self._lib.rtb_fit_field(self._ctx, kind, ptrs[0], len(y), ptrs[1], len(x), ptrs[2],
+                                            float(fit["delta"]), C.byref(stats)))
+        fit["stats"] = self._stats(stats)
+        self._field_key = key
+        self._keep = fit
+
+    def fit_field(self, x, y, Z, delta):
+        """interpolacion(x, y, Z) (RT_bench.py:435-464) on the GPU: np.gradient + the three spline fits + upload in
+        one call (rtb_fit_field).  x, y, Z: numpy arrays, or torch CUDA tensors on this engine's device.
+        Returns (z, (grd0, grd1)) DeviceSpline handles that trazar / search_delta / n_gradient accept."""
+        if _is_torch(Z):
+            import torch
+            x, y, Z = (t.to(dtype=torch.float64).contiguous() for t in (x, y, Z))
+            shape = tuple(Z.shape)
+        else:
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            y = np.ascontiguousarray(y, dtype=np.float64)
+            Z = np.ascontiguousarray(Z, dtype=np.float64)
+            shape = Z.shape
+        if len(shape) != 2 or shape != (len(y), len(x)):
+            raise ValueError("fit_field: Z must have shape (len(y), len(x))")    # scipy raises the same way
+        fit = dict(engine=self, x=x, y=y, Z=Z, delta=float(delta), tck={})
+        self._ensure_fit(fit)
+        return DeviceSpline(fit, 0), (DeviceSpline(fit, 1), DeviceSpline(fit, 2))
+
+    def gradient(self, Z, delta):
+        """np.gradient(Z, delta, edge_order=2) (RT_bench.py:449) -> [d/d axis0, d/d axis1], bit-exact."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        g0, g1 = np.empty_like(Z), np.empty_like(Z)
+        self._check(self._lib.rtb_gradient(self._ctx, _cabi.RTB_PTR_HOST, Z.ctypes.data, Z.shape[0], Z.shape[1],
+                                           float(delta), g0.ctypes.data, g1.ctypes.data))
+        return [g0, g1]
+
+    def get_field(self, which):
+        """(tu, tv, c) of the resident field: 0 = z, 1 = grd[0], 2 = grd[1] (scipy's .tck layout)."""
+        nu, nv = C.c_int32(), C.c_int32()
+        self._check(self._lib.rtb_get_field(self._ctx, which, C.byref(nu), C.byref(nv), None, None, None))
+        k = 1 if which == 0 else 3
+        tu, tv = np.empty(nu.value), np.empty(nv.value)
+        c = np.empty((nu.value - k - 1) * (nv.value - k - 1))
+        self._check(self._lib.rtb_get_field(self._ctx, which, None, None, tu.ctypes.data, tv.ctypes.data,
+                                            c.ctypes.data))
+        return tu, tv, c
 
     def fp64_peak(self):
         v = C.c_double()
