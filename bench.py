@@ -31,8 +31,8 @@ RAYS_PER_GPU = 1 << 20
 # instructions per warp-step.  The algorithmic figure of SURVEY.md 8(d) (376 flop: B-spline-form field evaluation,
 # 25 flop per sin or cos) is larger than what the kernel executes, so `roofline.frac` can exceed 1; the executed
 # figures below are the hardware-side view of the same launch.
-NCU_OP6 = {"dfma": 64.1, "dmul": 24.3, "dadd": 17.3, "l1_data_pipe_frac": 0.84, "fp64_pipe_active_frac": 0.606,
-           "source": "profiles/r1f_ncu_full_op6_fisheye1M.csv"}
+NCU_OP6 = {"dfma": 64.1, "dmul": 24.3, "dadd": 17.3, "l1_data_pipe_frac": 0.52, "fp64_pipe_active_frac": 0.628,
+           "source": "profiles/r1g_ncu_full_op6_fisheye1M.csv"}
 METRIC = "fp64_ray_steps_per_s"
 UNIT = "ray-steps/s"
 
@@ -274,7 +274,8 @@ def run_cuda(args):
                                             "MEASURED_PEAKS.json has no FP64 figure"},
                 "e2e": {"value": e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps,
-                        "api": "Engine.trace with pinned host numpy buffers (RTB_PTR_HOST)"},
+                        "api": "Engine.trace with pinned host numpy buffers (RTB_PTR_HOST): rtb_trace pipelines the fan in 8 chunks "
+                               "(H2D copy, kernel, D2H copy on three streams)"},
                 "gpu_launches": launches, "clocks": clocks}
         if full_info:
             full_info.update({"hbm_peak_gbs": hbm_peak, "hbm_frac": full_info["hbm_write_gbs"] / hbm_peak,

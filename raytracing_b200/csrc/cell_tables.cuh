@@ -1,4 +1,4 @@
-// cell_tables.cuh -- expands the three splines of the field into per-cell polynomials (DevField::pg, pn).
+// cell_tables.cuh -- expands the three splines of the field into per-cell polynomials (DevField::pg).
 //
 // On the uniform part of the grid the bicubic gradient splines (FITPACK form: one coefficient per knot, 16
 // of them weighted by two cubic B-spline bases per evaluation, RT_bench.py:153-155) and the bilinear n are,
@@ -20,7 +20,7 @@ __constant__ double kW[4][4] = {{1.0 / 48.0, -1.0 / 8.0, 1.0 / 4.0, -1.0 / 6.0},
                                 {1.0 / 48.0, 1.0 / 8.0, 1.0 / 4.0, 1.0 / 6.0}};
 
 // One thread per cell (lu, lv) of the fast region.
-__global__ void cell_table_kernel(DevField f, double2 *pg, double *pn)
+__global__ void cell_table_kernel(DevField f, double2 *pg)
 {
     const int nv = f.fhi_v - f.flo_v + 1, nu = f.fhi_u - f.flo_u + 1;
     const size_t ci = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -30,10 +30,10 @@ __global__ void cell_table_kernel(DevField f, double2 *pg, double *pn)
     {
         const double *c = f.cz + (size_t)(lu - 2) * f.ncz + (lv - 2);
         const double c00 = c[0], c01 = c[1], c10 = c[f.ncz], c11 = c[f.ncz + 1];
-        pn[4 * ci + 0] = 0.25 * ((c00 + c01) + (c10 + c11));
-        pn[4 * ci + 1] = 0.5 * ((c10 - c00) + (c11 - c01)); // d/dtu (u = first spline axis = physical y)
-        pn[4 * ci + 2] = 0.5 * ((c01 - c00) + (c11 - c10)); // d/dtv
-        pn[4 * ci + 3] = (c00 - c01) - (c10 - c11);
+        pg[RTB_CELL_REC * ci + 16] = make_double2(0.25 * ((c00 + c01) + (c10 + c11)),
+                                                   0.5 * ((c10 - c00) + (c11 - c01))); // n0, d/dtu (u = physical y)
+        pg[RTB_CELL_REC * ci + 17] = make_double2(0.5 * ((c01 - c00) + (c11 - c10)),     // d/dtv
+                                                   (c00 - c01) - (c10 - c11));
     }
     // bicubic pair: m[p][q] = sum_a sum_b kW[a][p] c[a][b] kW[b][q]
     const double2 *c = f.cg + (size_t)(lu - 3) * f.ncg + (lv - 3);
@@ -55,7 +55,7 @@ __global__ void cell_table_kernel(DevField f, double2 *pg, double *pn)
             double2 m;
             m.x = fma(cq[3][q].x, kW[3][p], fma(cq[2][q].x, kW[2][p], fma(cq[1][q].x, kW[1][p], cq[0][q].x * kW[0][p])));
             m.y = fma(cq[3][q].y, kW[3][p], fma(cq[2][q].y, kW[2][p], fma(cq[1][q].y, kW[1][p], cq[0][q].y * kW[0][p])));
-            pg[16 * ci + 4 * p + q] = m;
+            pg[RTB_CELL_REC * ci + 4 * p + q] = m;
         }
 }
 

@@ -34,6 +34,9 @@ struct rtb_ctx {
     std::vector<void *> field_allocs;
     unsigned long long *d_total = nullptr;
     int block = RTB_BLOCK;
+    // host-buffer calls on large fans are cut into chunks whose H2D copy, kernel and D2H copy overlap (rtb_trace)
+    cudaStream_t pipe[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // fork + one join per pipe stream
     std::string err;
     // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
     struct PoolBuf { void *p; size_t bytes; bool used; };
@@ -81,12 +84,14 @@ static inline CellBox make_cell_box(const DevField &f, double limx_i, double lim
 struct Staging {
     rtb_ctx *ctx;
     bool host;
+    cudaStream_t stream;
     std::vector<void *> tmp;
-    struct Back { void *host; void *dev; size_t bytes; };
+    struct Back { void *host; void *dev; size_t bytes; size_t rows, host_pitch, dev_pitch; };
     std::vector<Back> back;
     int64_t h2d = 0, d2h = 0;
     cudaError_t err = cudaSuccess;
-    Staging(rtb_ctx *c, bool h) : ctx(c), host(h) {}
+    Staging(rtb_ctx *c, bool h) : ctx(c), host(h), stream(c->stream) {}
+    Staging(rtb_ctx *c, bool h, cudaStream_t s) : ctx(c), host(h), stream(s) {}
     ~Staging()
     {
         for (void *p : tmp)
@@ -120,7 +125,7 @@ struct Staging {
         if (!p || !host) return p;
         void *d = alloc(count * sizeof(T));
         if (!d) return nullptr;
-        cudaError_t e = cudaMemcpyAsync(d, p, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream);
+        cudaError_t e = cudaMemcpyAsync(d, p, count * sizeof(T), cudaMemcpyHostToDevice, stream);
         if (e != cudaSuccess) err = e;
         h2d += (int64_t)(count * sizeof(T));
         return (const T *)d;
@@ -130,15 +135,26 @@ struct Staging {
         if (!p || !host) return p;
         void *d = alloc(count * sizeof(T));
         if (!d) return nullptr;
-        back.push_back({p, d, count * sizeof(T)});
+        back.push_back({p, d, count * sizeof(T), 1, 0, 0});
+        return (T *)d;
+    }
+    // Columns [col0, col0+cols) of a host array of `rows` rows of `pitch` elements: a dense (rows, cols) device array.
+    template <class T> T *out_cols(T *p, size_t rows, size_t pitch, size_t col0, size_t cols)
+    {
+        if (!p) return nullptr;
+        void *d = alloc(rows * cols * sizeof(T));
+        if (!d) return nullptr;
+        back.push_back({p + col0, d, cols * sizeof(T), rows, pitch * sizeof(T), cols * sizeof(T)});
         return (T *)d;
     }
     void copy_back()
     {
         for (auto &b : back) {
-            cudaError_t e = cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, ctx->stream);
+            cudaError_t e = b.rows == 1
+                ? cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, stream)
+                : cudaMemcpy2DAsync(b.host, b.host_pitch, b.dev, b.dev_pitch, b.bytes, b.rows, cudaMemcpyDeviceToHost, stream);
             if (e != cudaSuccess) err = e;
-            d2h += (int64_t)b.bytes;
+            d2h += (int64_t)(b.bytes * b.rows);
         }
     }
 };

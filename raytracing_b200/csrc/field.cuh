@@ -42,18 +42,19 @@ struct DevField {
     int fast_ok, flo_u, fhi_u, flo_v, fhi_v;
     // Per-cell polynomial tables of the fast region (built on the device by rtb_set_field, cell_tables.cuh): for
     // the cell (lu, lv), ci = (lu - flo_u) * pstride + (lv - flo_v),
-    //   pg[16*ci + 4*p + q] = coefficient of tu^p tv^q of {dn/dy, dn/dx}   (tu, tv in [-1/2, 1/2]: offsets from the
-    //   pn[4*ci + ..]       = n0, d/dtu, d/dtv, d2/dtu dtv of the bilinear n        cell centre in cell units)
+    //   pg[18*ci + 4*p + q] = coefficient of tu^p tv^q of {dn/dy, dn/dx}   (tu, tv in [-1/2, 1/2]: offsets from the
+    //   pg[18*ci + 16, 17]  = {n0, d/dtu}, {d/dtv, d2/dtu dtv} of the bilinear n    cell centre in cell units)
     // i.e. the same piecewise polynomials as the B-spline form, expanded once: 33 FP64 instructions per evaluation
     // instead of 66 (two cubic bases + 32 coefficient MACs + bilinear), for 288 B of table per cell (L2 / HBM).
     const double2 *pg;
-    const double *pn;
     int pstride;
 };
 
 // Cubic-interval index ranges (inclusive) inside which a position needs no further checks in the step loop:
 // the default evaluator's fast region intersected with the cells that lie strictly inside the box of
 // constants() (RT:878), so the common case pays neither the general-path test nor the four FP64 box compares.
+constexpr int RTB_CELL_REC = 18; // double2 per cell record
+
 struct CellBox { int lo_u, hi_u, lo_v, hi_v; };
 
 // FITPACK fpbisp interval search, restated for the GPU: clamp, then find l (0-based) with
@@ -181,12 +182,39 @@ static __device__ __noinline__ FieldSample n_gradient_general(const DevField *fd
     return r;
 }
 
+// One cell record (RTB_CELL_REC double2: 16 bicubic-pair coefficients + 4 bilinear ones) evaluated at the offsets
+// (tu, tv) from the cell centre: Horner in tv for each power of tu, both gradient components at once.
+template <bool SMEM>
+__device__ __forceinline__ void eval_record(const double2 *c, double tu, double tv, double &n, double &gx, double &gy)
+{
+    auto ld = [&](int k) { return SMEM ? c[k] : __ldg(c + k); };
+    {
+        const double2 a = ld(16), b = ld(17); // {n0, n_u}, {n_v, n_uv}
+        n = fma(tu, fma(tv, b.y, a.y), fma(tv, b.x, a.x));
+    }
+    double2 row[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const double2 c0 = ld(4 * p), c1 = ld(4 * p + 1), c2 = ld(4 * p + 2), c3 = ld(4 * p + 3);
+        row[p].x = fma(fma(fma(c3.x, tv, c2.x), tv, c1.x), tv, c0.x);
+        row[p].y = fma(fma(fma(c3.y, tv, c2.y), tv, c1.y), tv, c0.y);
+    }
+    gy = fma(fma(fma(row[3].x, tu, row[2].x), tu, row[1].x), tu, row[0].x);
+    gx = fma(fma(fma(row[3].y, tu, row[2].y), tu, row[1].y), tu, row[0].y);
+}
 // Default evaluator: one interval computation per physical axis without knot comparisons (a position 1e-13 of
 // a cell beyond a knot evaluates the neighbouring polynomial piece of a C2 / C0 spline: error << 1e-13), then the
 // cell's expanded polynomials from the tables.  Falls back to the general routine outside the fast region.
 // Returns true when the position's cell lies inside `in` (then it is also strictly inside the box).
+//
+// Warp staging (wbuf != nullptr, dense fans): when all 32 lanes of the warp are stepping (mask full) and sit in the
+// SAME cell -- neighbouring rays of a 2^20-ray fan are ~1e-5 cells apart -- 18 lanes fetch the record once (one
+// LDG.128), park it in the warp's 288 B of shared memory and every lane reads it back with broadcast LDS.128: the
+// L1 data pipe moves 32 lanes x 16 B per LDG.128 whatever the addresses are (4 wavefronts, tools/lsu_microbench.cu),
+// a uniform LDS.128 costs half of that.  Same table entries, same arithmetic, same results.
 __device__ __forceinline__ bool n_gradient_cells(const DevField &f, const DevField *fd, const CellBox &in, double x,
-                                                 double y, double &n, double &gx, double &gy)
+                                                 double y, double &n, double &gx, double &gy, unsigned mask = 0u,
+                                                 double2 *wbuf = nullptr)
 {
     // Interval index and cell fraction without conversion instructions or knot loads: vh = (interval
     // coordinate) - 0.5; adding 1.5*2^52 rounds it to the nearest integer = floor(coordinate), which then sits in
@@ -200,6 +228,21 @@ __device__ __forceinline__ bool n_gradient_cells(const DevField &f, const DevFie
     // |coordinate| < 2^31 <=> high word of the sum is 0x43380000 (or 0x4337ffff for negatives); NaN fails too
     const bool sane = (unsigned)(__double2hiint(mu) - 0x4337ffff) <= 1u && (unsigned)(__double2hiint(mv) - 0x4337ffff) <= 1u;
     const bool inner = sane && lu >= in.lo_u && lu <= in.hi_u && lv >= in.lo_v && lv <= in.hi_v;
+#ifndef RTB_NO_STAGE
+    if (wbuf != nullptr && mask == 0xffffffffu) { // warp-uniform condition
+        const int cell = inner ? (lu - f.flo_u) * f.pstride + (lv - f.flo_v) : -1;
+        const int cell0 = __shfl_sync(0xffffffffu, cell, 0);
+        if (__all_sync(0xffffffffu, cell == cell0 && cell >= 0)) {
+            const int lane = threadIdx.x & 31;
+            __syncwarp(); // the previous record has been read by every lane
+            if (lane < RTB_CELL_REC) wbuf[lane] = __ldg(f.pg + (size_t)RTB_CELL_REC * cell0 + lane);
+            __syncwarp();
+            const double tu = vu - (mu - MAGIC), tv = vv - (mv - MAGIC);
+            eval_record<true>(wbuf, tu, tv, n, gx, gy);
+            return true;
+        }
+    }
+#endif
     if (!inner) { // rare: near the box / grid edge, or arbitrary knots
         if (!f.fast_ok || !sane || lu < f.flo_u || lu > f.fhi_u || lv < f.flo_v || lv > f.fhi_v) {
             const FieldSample r = n_gradient_general(fd, x, y);
@@ -209,21 +252,8 @@ __device__ __forceinline__ bool n_gradient_cells(const DevField &f, const DevFie
     }
     const double tu = vu - (mu - MAGIC), tv = vv - (mv - MAGIC); // offsets from the cell centre, in [-1/2, 1/2]
     const size_t ci = (size_t)(lu - f.flo_u) * f.pstride + (lv - f.flo_v);
-    {
-        const double2 *c = reinterpret_cast<const double2 *>(f.pn + 4 * ci);
-        const double2 a = __ldg(c), b = __ldg(c + 1); // {n0, n_u}, {n_v, n_uv}
-        n = fma(tu, fma(tv, b.y, a.y), fma(tv, b.x, a.x));
-    }
-    const double2 *c = f.pg + 16 * ci;
-    double2 row[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p) { // Horner in tv for each power of tu, both gradient components at once
-        const double2 c0 = __ldg(c + 4 * p), c1 = __ldg(c + 4 * p + 1), c2 = __ldg(c + 4 * p + 2), c3 = __ldg(c + 4 * p + 3);
-        row[p].x = fma(fma(fma(c3.x, tv, c2.x), tv, c1.x), tv, c0.x);
-        row[p].y = fma(fma(fma(c3.y, tv, c2.y), tv, c1.y), tv, c0.y);
-    }
-    gy = fma(fma(fma(row[3].x, tu, row[2].x), tu, row[1].x), tu, row[0].x);
-    gx = fma(fma(fma(row[3].y, tu, row[2].y), tu, row[1].y), tu, row[0].y);
+    const double2 *c = f.pg + (size_t)RTB_CELL_REC * ci;
+    eval_record<false>(c, tu, tv, n, gx, gy);
     return inner;
 }
 

@@ -48,6 +48,8 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
     if (ctx->d_total) cudaFree(ctx->d_total);
     for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    for (auto &ps : ctx->pipe) if (ps) cudaStreamDestroy(ps);
+    for (auto &pe : ctx->pipe_ev) if (pe) cudaEventDestroy(pe);
     delete ctx;
 }
 
@@ -132,16 +134,14 @@ int rtb_finish_field(rtb_ctx *ctx, DevField &f, const double *tzu, int nzu, cons
     f.fast_ok = shared_axis(tzu, nzu, f.zu, tgu, f.gu_, f.flo_u, f.fhi_u) &&
                 shared_axis(tzv, nzv, f.zv, tgv, f.gv_, f.flo_v, f.fhi_v);
     // per-cell polynomial tables of the fast region (cell_tables.cuh); without them the general evaluator is used
-    f.pg = nullptr; f.pn = nullptr; f.pstride = 0;
+    f.pg = nullptr; f.pstride = 0;
     if (f.fast_ok) {
         const size_t ncell = (size_t)(f.fhi_u - f.flo_u + 1) * (size_t)(f.fhi_v - f.flo_v + 1);
         double2 *pg = nullptr;
-        double *pn = nullptr;
-        if (cudaMalloc(&pg, ncell * 16 * sizeof(double2)) == cudaSuccess) ctx->field_allocs.push_back(pg);
-        if (pg && cudaMalloc(&pn, ncell * 4 * sizeof(double)) == cudaSuccess) ctx->field_allocs.push_back(pn);
-        if (pg && pn) {
-            f.pg = pg; f.pn = pn; f.pstride = f.fhi_v - f.flo_v + 1;
-            cell_table_kernel<<<(unsigned)((ncell + 127) / 128), 128, 0, ctx->stream>>>(f, pg, pn);
+        if (cudaMalloc(&pg, ncell * RTB_CELL_REC * sizeof(double2)) == cudaSuccess) ctx->field_allocs.push_back(pg);
+        if (pg) {
+            f.pg = pg; f.pstride = f.fhi_v - f.flo_v + 1;
+            cell_table_kernel<<<(unsigned)((ncell + 127) / 128), 128, 0, ctx->stream>>>(f, pg);
             CK(cudaGetLastError());
             CK(cudaStreamSynchronize(ctx->stream));
         } else {
@@ -274,6 +274,42 @@ __global__ void snell_from_cap_kernel(const double *cap, const double *theta0, i
 // ---------------------------------------------------------------------------------------
 // rtb_trace: trazar RT_bench.py:766-948
 // ---------------------------------------------------------------------------------------
+// The kernels of one trace on stream `st`, every pointer of `a` on the device: the integration and, when asked, the
+// Snell error metric (RT_bench.py:896-919).
+static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const TraceArgs &a, double *d_err,
+                      bool has_errors, bool want_err, bool traj, int stride, Staging &sg, int64_t &launches)
+{
+    const int64_t R = a.R;
+    const bool iso = p->gamma == 1.0;
+    const bool exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
+    CK(kLaunch[p->method](a, iso, traj, exact, ctx->block, st));
+    ++launches;
+    const unsigned g1 = (unsigned)((R + 127) / 128);
+    if (has_errors) {
+        if (!want_err) {
+            CK(cudaMemsetAsync(d_err, 0, sizeof(double) * R, st));
+        } else if (traj && stride == 1) {
+            snell_from_traj_kernel<<<g1, 128, 0, st>>>(a.s_ray, a.d_ray, a.theta0, R, d_err);
+            ++launches;
+        } else {
+            // two-pass: the sample rows int(9i/10), int(9.5i/10) depend on the final step count i,
+            // so re-integrate (bit-identical arithmetic) up to the later row and capture both.
+            int *cap_rows = (int *)sg.alloc(sizeof(int) * 2 * R);
+            double *cap_out = (double *)sg.alloc(sizeof(double) * 4 * R);
+            if (!cap_rows || !cap_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_trace: capture buffers", sg.err);
+            snell_rows_kernel<<<g1, 128, 0, st>>>(a.d_ray, R, cap_rows);
+            TraceArgs b = a;
+            b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr;
+            b.total_steps = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
+            CK(kLaunch[p->method](b, iso, false, exact, ctx->block, st));
+            snell_from_cap_kernel<<<g1, 128, 0, st>>>(cap_out, a.theta0, R, d_err);
+            launches += 3;
+        }
+        CK(cudaGetLastError());
+    }
+    return RTB_OK;
+}
+
 extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0,
                          const double *y0, int64_t R, double *s_ray, double *d_ray, double *errors,
                          double *last_row, double *px_stats, rtb_stats *stats)
@@ -297,71 +333,99 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     const int64_t rows = traj ? (p->max_size + stride - 1) / stride : 0;
 
     CK(cudaEventRecord(ctx->ev[0], st));
-    Staging sg(ctx, host);
-    TraceArgs a;
-    std::memset(&a, 0, sizeof(a));
-    a.f = ctx->f;
-    a.f_dev = ctx->f_dev;
-    a.theta0 = sg.in(theta0, R); a.x0 = sg.in(x0, R); a.y0 = sg.in(y0, R);
-    a.steps = sg.in(p->steps, R); a.max_sizes = sg.in(p->max_sizes, R);
-    a.R = R; a.max_size = (int)p->max_size; a.out_stride = stride;
-    a.tail_zero = (p->flags & RTB_F_NO_TAIL_ZERO) ? 0 : 1;
-    a.step = p->step; a.gamma = p->gamma;
-    a.limx_i = p->limx_i; a.limx_s = p->limx_s; a.limy_i = p->limy_i; a.limy_s = p->limy_s;
-    a.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
-    a.s_ray = sg.out(s_ray, (size_t)rows * 6 * R);
-    a.d_ray = sg.out(d_ray, (size_t)3 * R);
-    a.last_row = sg.out(last_row, (size_t)6 * R);
-    a.px_stats = sg.out(px_stats, (size_t)3 * R);
-    double *d_err = sg.out(errors, (size_t)R);
-    a.total_steps = ctx->d_total;
-    if (sg.err != cudaSuccess) return fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
-                                            "rtb_trace: staging", sg.err);
     CK(cudaMemsetAsync(ctx->d_total, 0, sizeof(unsigned long long), st));
+    TraceArgs base;
+    std::memset(&base, 0, sizeof(base));
+    base.f = ctx->f;
+    base.f_dev = ctx->f_dev;
+    base.max_size = (int)p->max_size; base.out_stride = stride;
+    base.tail_zero = (p->flags & RTB_F_NO_TAIL_ZERO) ? 0 : 1;
+    base.step = p->step; base.gamma = p->gamma;
+    base.limx_i = p->limx_i; base.limx_s = p->limx_s; base.limy_i = p->limy_i; base.limy_s = p->limy_s;
+    base.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
+    base.total_steps = ctx->d_total;
+    int64_t launches = 0, h2d = 0, d2h = 0;
+    int rc;
 
-    const bool iso = p->gamma == 1.0;
-    const bool exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
-    int64_t launches = 0;
-    CK(cudaEventRecord(ctx->ev[1], st));
-    CK(kLaunch[p->method](a, iso, traj, exact, ctx->block, st));
-    ++launches;
-    const unsigned g1 = (unsigned)((R + 127) / 128);
-    if (errors) {
-        if (!want_err) {
-            CK(cudaMemsetAsync(d_err, 0, sizeof(double) * R, st));
-        } else if (traj && stride == 1) {
-            snell_from_traj_kernel<<<g1, 128, 0, st>>>(a.s_ray, a.d_ray, a.theta0, R, d_err);
-            ++launches;
-        } else {
-            // two-pass: the sample rows int(9i/10), int(9.5i/10) depend on the final step count i,
-            // so re-integrate (bit-identical arithmetic) up to the later row and capture both.
-            int *cap_rows = (int *)sg.alloc(sizeof(int) * 2 * R);
-            double *cap_out = (double *)sg.alloc(sizeof(double) * 4 * R);
-            if (!cap_rows || !cap_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_trace: capture buffers", sg.err);
-            snell_rows_kernel<<<g1, 128, 0, st>>>(a.d_ray, R, cap_rows);
-            TraceArgs b = a;
-            b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr;
-            b.total_steps = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
-            CK(kLaunch[p->method](b, iso, false, exact, ctx->block, st));
-            snell_from_cap_kernel<<<g1, 128, 0, st>>>(cap_out, a.theta0, R, d_err);
-            launches += 3;
+    // Host buffers, no trajectory, a large fan: cut the rays into chunks and run each chunk's H2D copy, kernels and
+    // D2H copy on one of three side streams, so that the copies of one chunk overlap the stepping of the others
+    // (rays are independent: the results are those of the single launch, bit for bit).
+    const int64_t kPipeMinRays = 1 << 17;
+    if (host && !traj && R >= kPipeMinRays) {
+        for (auto &ps : ctx->pipe) if (!ps) CK(cudaStreamCreateWithFlags(&ps, cudaStreamNonBlocking));
+        for (auto &pe : ctx->pipe_ev) if (!pe) CK(cudaEventCreateWithFlags(&pe, cudaEventDisableTiming));
+        const int64_t nchunk = std::min<int64_t>(8, R / (kPipeMinRays / 2));
+        const int64_t chunk = (((R + nchunk - 1) / nchunk) + 127) / 128 * 128;
+        CK(cudaEventRecord(ctx->ev[1], st));
+        CK(cudaEventRecord(ctx->pipe_ev[0], st));
+        for (auto &ps : ctx->pipe) CK(cudaStreamWaitEvent(ps, ctx->pipe_ev[0], 0));
+        std::vector<Staging> sgs;
+        sgs.reserve((size_t)nchunk);
+        int k = 0;
+        for (int64_t r0 = 0; r0 < R; r0 += chunk, ++k) {
+            const int64_t rn = std::min(chunk, R - r0);
+            cudaStream_t ps = ctx->pipe[k % 3];
+            sgs.emplace_back(ctx, true, ps);
+            Staging &sg = sgs.back();
+            TraceArgs a = base;
+            a.theta0 = sg.in(theta0 + r0, rn); a.x0 = sg.in(x0 + r0, rn); a.y0 = sg.in(y0 + r0, rn);
+            a.steps = sg.in(p->steps ? p->steps + r0 : nullptr, rn);
+            a.max_sizes = sg.in(p->max_sizes ? p->max_sizes + r0 : nullptr, rn);
+            a.R = rn;
+            a.d_ray = sg.out_cols(d_ray, 3, R, r0, rn);
+            a.last_row = sg.out_cols(last_row, 6, R, r0, rn);
+            a.px_stats = sg.out_cols(px_stats, 3, R, r0, rn);
+            double *d_err = sg.out(errors ? errors + r0 : nullptr, (size_t)rn);
+            if (sg.err != cudaSuccess) return fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
+                                                    "rtb_trace: staging", sg.err);
+            if ((rc = trace_core(ctx, ps, p, a, d_err, errors != nullptr, want_err, false, stride, sg, launches))) return rc;
+            sg.copy_back();
         }
-        CK(cudaGetLastError());
+        for (int j = 0; j < 3; ++j) {
+            CK(cudaEventRecord(ctx->pipe_ev[1 + j], ctx->pipe[j]));
+            CK(cudaStreamWaitEvent(st, ctx->pipe_ev[1 + j], 0));
+        }
+        CK(cudaEventRecord(ctx->ev[2], st));
+        unsigned long long total = 0;
+        CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(ctx->ev[3], st));
+        CK(cudaStreamSynchronize(st));
+        for (auto &sg : sgs) {
+            if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg.err);
+            h2d += sg.h2d; d2h += sg.d2h;
+        }
+        if (stats) stats->ray_steps = (int64_t)total;
+    } else {
+        Staging sg(ctx, host);
+        TraceArgs a = base;
+        a.theta0 = sg.in(theta0, R); a.x0 = sg.in(x0, R); a.y0 = sg.in(y0, R);
+        a.steps = sg.in(p->steps, R); a.max_sizes = sg.in(p->max_sizes, R);
+        a.R = R;
+        a.s_ray = sg.out(s_ray, (size_t)rows * 6 * R);
+        a.d_ray = sg.out(d_ray, (size_t)3 * R);
+        a.last_row = sg.out(last_row, (size_t)6 * R);
+        a.px_stats = sg.out(px_stats, (size_t)3 * R);
+        double *d_err = sg.out(errors, (size_t)R);
+        if (sg.err != cudaSuccess) return fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
+                                                "rtb_trace: staging", sg.err);
+        CK(cudaEventRecord(ctx->ev[1], st));
+        if ((rc = trace_core(ctx, st, p, a, d_err, errors != nullptr, want_err, traj, stride, sg, launches))) return rc;
+        CK(cudaEventRecord(ctx->ev[2], st));
+        sg.copy_back();
+        unsigned long long total = 0;
+        CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(ctx->ev[3], st));
+        CK(cudaStreamSynchronize(st));
+        if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg.err);
+        h2d = sg.h2d; d2h = sg.d2h;
+        if (stats) stats->ray_steps = (int64_t)total;
     }
-    CK(cudaEventRecord(ctx->ev[2], st));
-    sg.copy_back();
-    unsigned long long total = 0;
-    CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(ctx->ev[3], st));
-    CK(cudaStreamSynchronize(st));
-    if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg.err);
     if (stats) {
         float ms = 0;
         cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); stats->kernel_ms = ms;
         cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); stats->total_ms = ms;
-        stats->ray_steps = (int64_t)total;
         stats->launches = launches;
-        stats->h2d_bytes = sg.h2d; stats->d2h_bytes = sg.d2h;
+        stats->h2d_bytes = h2d; stats->d2h_bytes = d2h;
     }
     return RTB_OK;
 }

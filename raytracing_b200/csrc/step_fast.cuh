@@ -139,7 +139,7 @@ __device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_les
 template <int METHOD, bool ISO, bool LAZY>
 __device__ __forceinline__ double step_fast(const DevField &f, const DevField *fd, const CellBox &in, FastState &s, double h,
                                             double gamma, double g2m1, double (&hist)[3][2], int i, bool bootstrap,
-                                            bool &inner)
+                                            bool &inner, unsigned mask = 0u, double2 *wbuf = nullptr)
 {
     constexpr int ADV = advancer_of(METHOD);
     constexpr int UPD = updater_of(METHOD);
@@ -184,7 +184,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         }
     }
     double fn, fgx, fgy;
-    inner = n_gradient_cells(f, fd, in, fx, fy, fn, fgx, fgy); // true: new position strictly inside the box
+    inner = n_gradient_cells(f, fd, in, fx, fy, fn, fgx, fgy, mask, wbuf); // true: new position strictly inside the box
     const double inv_fn = rcp_fast3(fn);
     const double hn1 = h * inv_fn;
 

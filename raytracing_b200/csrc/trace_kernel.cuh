@@ -118,8 +118,11 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
     const int Mloop = TRAJ ? a.max_size : M;
     // The loop condition must be warp-uniform (lanes may have different M with per-ray max_sizes):
     // every lane iterates until no lane of the warp is alive; `alive` drops at i+1 >= M.
+    __shared__ double2 stage[EXACT ? 1 : RTB_BLOCK / 32][RTB_CELL_REC]; // one cell record per warp (field.cuh)
+    double2 *const wbuf = EXACT ? nullptr : stage[threadIdx.x >> 5];
     for (;; ++i) {
-        if (!__any_sync(0xffffffffu, alive)) break;
+        const unsigned mask = __ballot_sync(0xffffffffu, alive);
+        if (!mask) break;
         if (alive) {
             double dist;
             bool inner = false; // new position known to be strictly inside the box (no FP64 compares needed)
@@ -153,7 +156,7 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
                 moments_sc<ISO>(fn, s.coef, g2m1, s.ux, s.uy, px, py);
                 s.x = fx; s.y = fy; s.ang = fang; s.n = fn; s.gx = fgx; s.gy = fgy;
             } else {
-                dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, a.in, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3, inner);
+                dist = step_fast<METHOD, ISO, LAZY>(a.f, a.f_dev, a.in, s, h, gamma, g2m1, hist, i, METHOD == 7 && i < 3, inner, mask, wbuf);
                 if (TRAJ || EXTRA) moments_fast<ISO>(s, g2m1, px, py); // else only the last row's, after the loop
             }
             dist_sim += dist;

@@ -10,6 +10,8 @@ FL="-O3 -std=c++17 -lineinfo $ARCH -Xcompiler -fPIC -Xptxas -v $@"
 pids=()
 ( nvcc $FL -c $src/rtb.cu -o $out/rtb.o 2> $out/rtb.log ) & pids+=($!)
 ( nvcc $FL -c $src/shoot.cu -o $out/shoot.o 2> $out/shoot.log ) & pids+=($!)
+( nvcc $FL -c $src/wavefront.cu -o $out/wavefront.o 2> $out/wavefront.log ) & pids+=($!)
+( nvcc $FL -c $src/fit.cu -o $out/fit.o 2> $out/fit.log ) & pids+=($!)
 for m in 1 2 3 4 5 6 7 8 9 10 11; do
   ( nvcc $FL -DRTB_METHOD=$m -c $src/trace_inst.cu -o $out/trace_m$m.o 2> $out/trace_m$m.log ) & pids+=($!)
 done
