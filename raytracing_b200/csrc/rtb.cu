@@ -344,6 +344,7 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     base.limx_i = p->limx_i; base.limx_s = p->limx_s; base.limy_i = p->limy_i; base.limy_s = p->limy_s;
     base.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
     base.total_steps = ctx->d_total;
+    base.stage = R >= (1 << 16); // below ~one wave of warps a launch is a latency chain: no staging detour
     int64_t launches = 0, h2d = 0, d2h = 0;
     int rc;
 

@@ -145,25 +145,29 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
     constexpr int UPD = updater_of(METHOD);
     double fx, fy;
     bool ignore = true;
-    const double dot = fma(s.gx, s.ux, s.gy * s.uy);
-    const double qx = fma(-dot, s.ux, s.gx), qy = fma(-dot, s.uy, s.gy); // grad n minus its tangential part
+    // grad n minus its tangential part is (u x grad n) n^, n^ = (-uy, ux) (|u| = 1 to rounding): one signed scalar
+    // `cross` carries it, k1 = cross * h/n is the curvature times the step, and the second-order displacement is
+    // n^ * (h/2) k1.  The step length follows from the same identity: |u h + n^ w|^2 = h^2 + w^2.
+    const double cross = fma(s.ux, s.gy, -(s.uy * s.gx));
+    const double k1 = cross * s.hn;
+    double dist = h; // ADV == 1: the chord is the step itself
     if (ADV == 1) {
         fx = fma(s.ux, h, s.x);
         fy = fma(s.uy, h, s.y);
     } else if (ADV == 2 || bootstrap) {
-        const double q = 0.5 * h * s.hn;
-        fx = fma(qx, q, fma(s.ux, h, s.x));
-        fy = fma(qy, q, fma(s.uy, h, s.y));
+        const double w = (0.5 * h) * k1;
+        fx = fma(-s.uy, w, fma(s.ux, h, s.x));
+        fy = fma(s.ux, w, fma(s.uy, h, s.y));
+        if (UPD != 2 || bootstrap) dist = sqrt_pos(fma(w, w, h * h)); // UPD == 2 takes it from k1^2 below
     } else {
-        const double q2 = fma(qx, qx, qy * qy);
-        const double curv = sqrt_fast(q2) * s.inv_n;
+        const double curv = fabs(cross) * s.inv_n;
         if (curv < RTB_GOLD_TOL) {
             fx = fma(s.ux, h, s.x);
             fy = fma(s.uy, h, s.y);
             ignore = false;
         } else {
             const double d = curv * h;
-            const double sg = (s.gx * s.uy - s.gy * s.ux > 0) ? -1.0 : 1.0;
+            const double sg = (cross < 0) ? -1.0 : 1.0; // RT:360: -1 where gx*uy - gy*ux > 0
             const double e = sg * d;
             double ds, dc; // sin(t+e)-sin(t), cos(t+e)-cos(t)
             if (d <= RTB_SMALL_ANGLE_MAX) {
@@ -178,18 +182,18 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
                 ds = s1 - s.uy;
                 dc = c1 - s.ux;
             }
-            const double icurv = s.n * rsqrt_fast(q2);
-            fx = fma(sg * ds, icurv, s.x);
-            fy = fma(-sg * dc, icurv, s.y);
+            const double icurv = s.n * rcp_fast(cross); // signed radius: sg / curvature
+            fx = fma(ds, icurv, s.x);
+            fy = fma(-dc, icurv, s.y);
         }
+        const double dx = s.x - fx, dy = s.y - fy;
+        dist = sqrt_pos(fma(dx, dx, dy * dy));
     }
     double fn, fgx, fgy;
     inner = n_gradient_cells(f, fd, in, fx, fy, fn, fgx, fgy, mask, wbuf); // true: new position strictly inside the box
     const double inv_fn = rcp_fast3(fn);
     const double hn1 = h * inv_fn;
 
-    const double dx = s.x - fx, dy = s.y - fy;
-    const double dist = sqrt_pos(fma(dx, dx, dy * dy));
 
     if (UPD == 3 || bootstrap) { // finite differences RT:370-372, bootstrap RT:843-857
         double vx, vy;
@@ -225,7 +229,6 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         // per-step increment in practice) so the whole update is one basic block the scheduler can interleave
         // with the reciprocal / square-root chains; the rare cases (large curvature*step) and the periodic exact
         // resync of (sin, cos) with the accumulated angle are repaired in ONE conditional block afterwards.
-        const double k1 = (s.ux * s.gy - s.uy * s.gx) * s.hn;
         double s1, c1;
         rotate_small(s.uy, s.ux, k1, s1, c1);
         double k2 = (c1 * fgy - s1 * fgx) * hn1;
@@ -234,8 +237,16 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
         rotate_small(s1, c1, 0.5 * (k2 - k1), nuy, nux);
         const bool small = abs_lt_hi(k1, HI_2M8) && abs_lt_hi(k2, HI_2M8);
+        if (ADV == 2) { // |dx| = h sqrt(1 + (k1/2)^2) = h (1 + z/8 - z^2/128 + O(z^3 2^-10)), z = k1^2 < 2^-16
+            const double z = k1 * k1;
+            dist = fma(h, z * fma(z, -0.0078125, 0.125), h);
+        }
         if (!small || (i & RTB_RESYNC_MASK) == 0) {
             if (!small) {
+                if (ADV == 2) {
+                    const double w = (0.5 * h) * k1;
+                    dist = sqrt_pos(fma(w, w, h * h));
+                }
                 sincos_cw(s.ang + k1, s1, c1);
                 k2 = (c1 * fgy - s1 * fgx) * hn1;
                 ang = s.ang + 0.5 * (k1 + k2);

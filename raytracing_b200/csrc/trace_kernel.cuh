@@ -28,7 +28,7 @@ struct TraceArgs {
     int max_size;
     int out_stride;
     int tail_zero;
-    int interface_metric;      // unused in-kernel (kept for symmetry)
+    int stage;                 // 1: warp-staged cell records (field.cuh) -- set for large fans, where throughput counts
     double step, gamma;
     double limx_i, limx_s, limy_i, limy_s;
     double *s_ray;             // TRAJ only
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
     // The loop condition must be warp-uniform (lanes may have different M with per-ray max_sizes):
     // every lane iterates until no lane of the warp is alive; `alive` drops at i+1 >= M.
     __shared__ double2 stage[EXACT ? 1 : RTB_BLOCK / 32][RTB_CELL_REC]; // one cell record per warp (field.cuh)
-    double2 *const wbuf = EXACT ? nullptr : stage[threadIdx.x >> 5];
+    double2 *const wbuf = (EXACT || !a.stage) ? nullptr : stage[threadIdx.x >> 5];
     for (;; ++i) {
         const unsigned mask = __ballot_sync(0xffffffffu, alive);
         if (!mask) break;
