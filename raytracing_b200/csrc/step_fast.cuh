@@ -229,24 +229,28 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         // per-step increment in practice) so the whole update is one basic block the scheduler can interleave
         // with the reciprocal / square-root chains; the rare cases (large curvature*step) and the periodic exact
         // resync of (sin, cos) with the accumulated angle are repaired in ONE conditional block afterwards.
-        double s1, c1;
-        rotate_small(s.uy, s.ux, k1, s1, c1);
-        double k2 = (c1 * fgy - s1 * fgx) * hn1;
-        double ang = s.ang + 0.5 * (k1 + k2);
+        // k2 = grad n(new) x u(theta + k1) * h/n: with (sin, cos)(theta + k1) = u + (u cm + n^ sk), sk = sin k1,
+        // cm = cos k1 - 1, the cross product is crossF (1 + cm) - dotF sk -- no intermediate unit vector -- and the
+        // final direction is ONE rotation of u by (k1 + k2)/2.
+        const double z = k1 * k1;
+        const double sk = fma(k1 * z, fma(z, K_1_120, -K_SIXTH), k1);
+        const double cm = z * fma(z, K_1_24, -0.5);
+        const double crossF = fma(s.ux, fgy, -(s.uy * fgx)), dotF = fma(s.ux, fgx, s.uy * fgy);
+        double k2 = fma(-dotF, sk, fma(crossF, cm, crossF)) * hn1;
+        double half = 0.5 * (k1 + k2);
+        double ang = s.ang + half;
         double nuy, nux;
-        // theta_f = (theta + k1) + (k2 - k1)/2: the second rotation starts from (s1, c1) and is O(h^2)
-        rotate_small(s1, c1, 0.5 * (k2 - k1), nuy, nux);
+        rotate_small(s.uy, s.ux, half, nuy, nux);
         const bool small = abs_lt_hi(k1, HI_2M8) && abs_lt_hi(k2, HI_2M8);
-        if (ADV == 2) { // |dx| = h sqrt(1 + (k1/2)^2) = h (1 + z/8 - z^2/128 + O(z^3 2^-10)), z = k1^2 < 2^-16
-            const double z = k1 * k1;
+        if (ADV == 2) // |dx| = h sqrt(1 + (k1/2)^2) = h (1 + z/8 - z^2/128 + O(z^3 2^-10)), z = k1^2 < 2^-16
             dist = fma(h, z * fma(z, -0.0078125, 0.125), h);
-        }
         if (!small || (i & RTB_RESYNC_MASK) == 0) {
             if (!small) {
                 if (ADV == 2) {
                     const double w = (0.5 * h) * k1;
                     dist = sqrt_pos(fma(w, w, h * h));
                 }
+                double s1, c1;
                 sincos_cw(s.ang + k1, s1, c1);
                 k2 = (c1 * fgy - s1 * fgx) * hn1;
                 ang = s.ang + 0.5 * (k1 + k2);
