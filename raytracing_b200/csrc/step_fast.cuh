@@ -99,14 +99,18 @@ __device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_les
         Lc = fma(-Ls, el, Lc); Rc = fma(-Rs, er, Rc);
         Ls = t0; Rs = t1;
     }
-    double Lf = cost(Ls, Lc), Rf = cost(Rs, Rc);
+    // State of the loop: the kept probe W and the newest probe N (sin, cos, offset from theta, cost) and on which
+    // side N lies -- one conditional move of four doubles per iteration instead of shuffling a left and a right set.
+    double Ws = Ls, Wc = Lc, Wpsi = Lpsi, Wf = cost(Ls, Lc);
+    double Ns = Rs, Nc = Rc, Npsi = Rpsi, Nf = cost(Rs, Rc);
+    bool nl = false; // N is the left probe (c)
     int k = 0;
 #pragma unroll 1
     while (fabs(c - d) > RTB_GOLD_TOL) {
-        bool left = Lf < Rf; // RT:189: if func(c) < func(d): b = d  else: a = c
-        const double df = Lf - Rf;
-        if (df * df <= tie2 * fmax(Lf, Rf)) left = exact_less(c, d);
-        const double Ws = left ? Ls : Rs, Wc = left ? Lc : Rc, Wpsi = left ? Lpsi : Rpsi; // kept probe
+        bool left = nl ? (Nf < Wf) : (Wf < Nf); // RT:189: if func(c) < func(d): b = d  else: a = c
+        const double df = Nf - Wf;
+        if (df * df <= tie2 * fmax(Nf, Wf)) left = exact_less(c, d);
+        if (left == nl) { Ws = Ns; Wc = Nc; Wpsi = Npsi; Wf = Nf; } // the kept probe: c when b moves, d when a moves
         b = left ? d : b;
         a = left ? a : c;
         c = b - (b - a) * RTB_GOLD_RATIO;
@@ -114,23 +118,20 @@ __device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_les
         const int kk = min(k, RTB_GOLDEN_ROT_N - 1);
         const double2 r = kGoldenRot[kk];
         const double sgn = left ? -1.0 : 1.0; // the new probe lies left of the kept one when b moved
-        const double psi = (left ? c : d) - theta;
+        Npsi = (left ? c : d) - theta;
         const double sr = sgn * r.x;
         const double ns = fma(Wc, sr, Ws * r.y), nc = fma(-Ws, sr, Wc * r.y);
-        const double eps = psi - fma(sgn, kGoldenDelta[kk], Wpsi);
-        const double fs = fma(nc, eps, ns), fc = fma(-ns, eps, nc);
-        const double ff = cost(fs, fc);
-        // left: (L, R) <- (new, old L);  else: (L, R) <- (old R, new)
-        const double oLs = Ls, oLc = Lc, oLpsi = Lpsi, oLf = Lf;
-        Ls = left ? fs : Rs; Lc = left ? fc : Rc; Lpsi = left ? psi : Rpsi; Lf = left ? ff : Rf;
-        Rs = left ? oLs : fs; Rc = left ? oLc : fc; Rpsi = left ? oLpsi : psi; Rf = left ? oLf : ff;
+        const double eps = Npsi - fma(sgn, kGoldenDelta[kk], Wpsi);
+        Ns = fma(nc, eps, ns); Nc = fma(-ns, eps, nc);
+        Nf = cost(Ns, Nc);
+        nl = left;
         ++k;
     }
     const double th = (b + a) / 2.0;
-    // sin/cos of the result from the left probe (|offset| <= final bracket ~3e-8: second order is exact to 1e-23)
-    const double e = (th - theta) - Lpsi, e2h = 0.5 * e * e;
-    s_out = fma(-Ls, e2h, fma(Lc, e, Ls));
-    c_out = fma(-Lc, e2h, fma(-Ls, e, Lc));
+    // sin/cos of the result from the kept probe (|offset| <= final bracket ~3e-8: second order is exact to 1e-23)
+    const double e = (th - theta) - Wpsi, e2h = 0.5 * e * e;
+    s_out = fma(-Ws, e2h, fma(Wc, e, Ws));
+    c_out = fma(-Wc, e2h, fma(-Ws, e, Wc));
     return th;
 }
 
@@ -213,7 +214,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
             hist[1][0] = hist[2][0]; hist[1][1] = hist[2][1];
             hist[2][0] = fx; hist[2][1] = fy;
         }
-        const double r = rsqrt_fast(fma(vx, vx, vy * vy));
+        const double r = rsqrt_fast3(fma(vx, vx, vy * vy));
         s.ux = vx * r; s.uy = vy * r;
         s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux); // same value in every output mode
     } else if (ADV == 3 && !ignore) {
@@ -221,7 +222,7 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
     } else if (UPD == 1) { // theta_cost_t RT:393-407
         const double a = fma(0.5 * h, s.gx + fgx, s.n * s.ux);
         const double b = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
-        const double r = rsqrt_fast(fma(a, a, b * b));
+        const double r = rsqrt_fast3(fma(a, a, b * b));
         s.ux = a * r; s.uy = b * r;
         s.ang = LAZY ? __longlong_as_double(0x7ff8000000000000ll) : atan2(s.uy, s.ux);
     } else if (UPD == 2) { // tfinal_2o RT:374-391
