@@ -31,8 +31,8 @@ RAYS_PER_GPU = 1 << 20
 # instructions per warp-step.  The algorithmic figure of SURVEY.md 8(d) (376 flop: B-spline-form field evaluation,
 # 25 flop per sin or cos) is larger than what the kernel executes, so `roofline.frac` can exceed 1; the executed
 # figures below are the hardware-side view of the same launch.
-NCU_OP6 = {"dfma": 64.1, "dmul": 24.3, "dadd": 17.3, "l1_data_pipe_frac": 0.52, "fp64_pipe_active_frac": 0.628,
-           "source": "profiles/r1g_ncu_full_op6_fisheye1M.csv"}
+NCU_OP6 = {"dfma": 59.5, "dmul": 19.4, "dadd": 13.3, "l1_data_pipe_frac": 0.59, "fp64_pipe_active_frac": 0.637,
+           "dram_bytes_per_launch": 26.645e6 + 19.594e6, "source": "profiles/r1h_ncu_full_op6_fisheye1M.csv"}
 METRIC = "fp64_ray_steps_per_s"
 UNIT = "ray-steps/s"
 
@@ -260,7 +260,8 @@ def run_cuda(args):
                            "l2": "flushed (256 MiB write) between timed steps",
                            "parallelism": "rays sharded x%d, d_ray all_gather" % world if world > 1 else "1 GPU"},
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak / 1e12, "unit": "TFLOP/s",
-                             "frac": achieved / (fp64_peak / 1e12), "traffic": None,
+                             "frac": achieved / (fp64_peak / 1e12),
+                             "traffic": NCU_OP6["dram_bytes_per_launch"], "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum; the call's inputs + outputs are 101 MB, mostly absorbed by the 126 MB L2)",
                              "kernel": "trace_kernel<6,iso,final>", "kernel_ms": k_ms,
                              "flop_per_ray_step": K.F_ALG[METHOD],
                              "executed": {"fp64_inst_per_ray_step": NCU_OP6["dfma"] + NCU_OP6["dmul"] + NCU_OP6["dadd"],
