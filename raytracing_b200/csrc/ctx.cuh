@@ -57,6 +57,15 @@ static inline int fail(rtb_ctx *c, int code, const char *what, cudaError_t e = c
         if (e_ != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, #call, e_);     \
     } while (0)
 
+// Lanes per ray for a launch of R rays: 2^shift, the largest power of two (<= 32) that still fits the whole fan
+// into one wave of 16 warps per SM (148 SMs); 0 from ~76 k rays on.  Spread launches use 32-thread blocks.
+static inline int pick_lane_shift(int64_t R)
+{
+    int shift = 0;
+    while (shift < 5 && (R << (shift + 1)) <= (int64_t)148 * 16 * 32) ++shift;
+    return shift;
+}
+
 // Field construction pieces defined in rtb.cu and shared with fit.cu.
 void rtb_free_field(rtb_ctx *ctx);
 int rtb_make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax);

@@ -282,7 +282,8 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
     const int64_t R = a.R;
     const bool iso = p->gamma == 1.0;
     const bool exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
-    CK(kLaunch[p->method](a, iso, traj, exact, ctx->block, st));
+    const int block = a.lane_shift ? 32 : ctx->block;
+    CK(kLaunch[p->method](a, iso, traj, exact, block, st));
     ++launches;
     const unsigned g1 = (unsigned)((R + 127) / 128);
     if (has_errors) {
@@ -301,7 +302,7 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
             TraceArgs b = a;
             b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr;
             b.total_steps = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
-            CK(kLaunch[p->method](b, iso, false, exact, ctx->block, st));
+            CK(kLaunch[p->method](b, iso, false, exact, block, st));
             snell_from_cap_kernel<<<g1, 128, 0, st>>>(cap_out, a.theta0, R, d_err);
             launches += 3;
         }
@@ -402,6 +403,7 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
         a.theta0 = sg.in(theta0, R); a.x0 = sg.in(x0, R); a.y0 = sg.in(y0, R);
         a.steps = sg.in(p->steps, R); a.max_sizes = sg.in(p->max_sizes, R);
         a.R = R;
+        a.lane_shift = pick_lane_shift(R);
         a.s_ray = sg.out(s_ray, (size_t)rows * 6 * R);
         a.d_ray = sg.out(d_ray, (size_t)3 * R);
         a.last_row = sg.out(last_row, (size_t)6 * R);

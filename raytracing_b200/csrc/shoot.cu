@@ -38,7 +38,8 @@ int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n
     a.d_ray = b.d_ray;
     a.exit_out = b.exit_out;
     a.total_steps = ctx->d_total;
-    // small batches: 32-thread blocks spread the rays over all SMs
+    // small batches: rays spread over the warps of all SMs (pick_lane_shift), 32-thread blocks
+    a.lane_shift = pick_lane_shift(n);
     const int block = n < (int64_t)148 * 4 * 128 ? 32 : ctx->block;
     cudaError_t e = kLaunch[p->method](a, p->gamma == 1.0, false, (p->flags & RTB_F_EXACT_BASIS) != 0, block, ctx->stream);
     if (e != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "shoot: trace launch", e);

@@ -28,6 +28,7 @@ struct TraceArgs {
     int max_size;
     int out_stride;
     int tail_zero;
+    int lane_shift;            // small fans: one ray per 2^lane_shift lanes (the others idle), see pick_lane_shift
     int stage;                 // 1: warp-staged cell records (field.cuh) -- set for large fans, where throughput counts
     double step, gamma;
     double limx_i, limx_s, limy_i, limy_s;
@@ -61,9 +62,13 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
 {
     constexpr int UPD = updater_of(METHOD);
     constexpr bool LAZY = !EXACT && !TRAJ && (UPD == 1 || UPD == 3); // theta evaluated once at the end
-    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = r < a.R;
-    const int64_t rr = valid ? r : a.R - 1; // padded lanes shadow the last ray, never store
+    // Small fans are spread one ray per 2^lane_shift lanes (up to one ray per warp): the step loop of a lone ray is a
+    // dependent chain, and 32 rays that sit in 32 different cells make every table load of their warp 32 cache
+    // lines wide; spread out, each ray gets a scheduler slot of its own and the fan covers all SMs.
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = gt >> a.lane_shift;
+    const bool valid = r < a.R && (gt & ((1 << a.lane_shift) - 1)) == 0;
+    const int64_t rr = r < a.R ? r : a.R - 1; // idle and padded lanes shadow a ray, never step or store
     const double h = a.steps ? a.steps[rr] : a.step;
     int M = a.max_sizes ? (int)a.max_sizes[rr] : a.max_size;
     const double gamma = a.gamma;
@@ -263,7 +268,7 @@ typedef cudaError_t (*launch_fn)(const TraceArgs &, bool iso, bool traj, bool ex
 template <int METHOD>
 cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
 {
-    const unsigned grid = (unsigned)((a.R + block - 1) / block);
+    const unsigned grid = (unsigned)(((a.R << a.lane_shift) + block - 1) / block);
     const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr;
 #define RTB_L(I, T, E)                                                                  \
     do {                                                                                \

@@ -147,3 +147,22 @@ def test_sharded_equals_unsharded(engine):
             parts.append(engine.trace(6, *a, s["step"], s["M"], s["gamma"], s["box"], full=False))
         assert np.array_equal(np.concatenate([p.d_ray for p in parts], 1), whole.d_ray)
         assert np.array_equal(np.concatenate([p.last_row for p in parts], 1), whole.last_row)
+
+
+@pytest.mark.parametrize("uc,m", [("2", 6), ("1", 4), ("4", 11)])
+def test_warp_staged_records_equal_per_lane_loads(engine, uc, m):
+    """Fans of >= 2^16 rays read the cell record once per warp through shared memory (field.cuh, warp staging);
+    smaller launches load it per lane.  Same table, same arithmetic: tracing a dense fan whole (staged) and in two
+    halves (per lane) must agree bit for bit, trajectories included."""
+    import raytracing_b200 as rt
+    s = scenario_setup(uc)
+    engine.set_field(s["z"], s["grd"])
+    R = 1 << 16
+    M = min(s["M"], 400)
+    th, x0, y0 = rt.make_fan(uc, R)
+    whole = engine.trace(m, th, x0, y0, s["step"], M, s["gamma"], s["box"], full=True, out_stride=57)
+    halves = [engine.trace(m, th[a:b], x0[a:b], y0[a:b], s["step"], M, s["gamma"], s["box"], full=True, out_stride=57)
+              for a, b in ((0, R // 2), (R // 2, R))]
+    for name in ("d_ray", "last_row"):
+        assert np.array_equal(np.concatenate([h[name] for h in halves], 1), whole[name], equal_nan=True), name
+    assert np.array_equal(np.concatenate([h.s_ray for h in halves], 2), whole.s_ray, equal_nan=True)
