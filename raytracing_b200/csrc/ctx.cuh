@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -101,6 +102,8 @@ struct Staging {
     cudaError_t err = cudaSuccess;
     Staging(rtb_ctx *c, bool h) : ctx(c), host(h), stream(c->stream) {}
     Staging(rtb_ctx *c, bool h, cudaStream_t s) : ctx(c), host(h), stream(s) {}
+    Staging(const Staging &) = delete; // the destructor hands the buffers back to the pool
+    Staging &operator=(const Staging &) = delete;
     ~Staging()
     {
         for (void *p : tmp)

@@ -361,14 +361,18 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
         CK(cudaEventRecord(ctx->ev[1], st));
         CK(cudaEventRecord(ctx->pipe_ev[0], st));
         for (auto &ps : ctx->pipe) CK(cudaStreamWaitEvent(ps, ctx->pipe_ev[0], 0));
-        std::vector<Staging> sgs;
-        sgs.reserve((size_t)nchunk);
+        // On any failure the side streams are drained before the staging buffers go back to the pool (`bail`).
+        std::vector<std::unique_ptr<Staging>> sgs;
+        auto bail = [&](int code) {
+            for (auto &ps : ctx->pipe) cudaStreamSynchronize(ps);
+            return code;
+        };
         int k = 0;
         for (int64_t r0 = 0; r0 < R; r0 += chunk, ++k) {
             const int64_t rn = std::min(chunk, R - r0);
             cudaStream_t ps = ctx->pipe[k % 3];
-            sgs.emplace_back(ctx, true, ps);
-            Staging &sg = sgs.back();
+            sgs.emplace_back(new Staging(ctx, true, ps));
+            Staging &sg = *sgs.back();
             TraceArgs a = base;
             a.theta0 = sg.in(theta0 + r0, rn); a.x0 = sg.in(x0 + r0, rn); a.y0 = sg.in(y0 + r0, rn);
             a.steps = sg.in(p->steps ? p->steps + r0 : nullptr, rn);
@@ -378,23 +382,27 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
             a.last_row = sg.out_cols(last_row, 6, R, r0, rn);
             a.px_stats = sg.out_cols(px_stats, 3, R, r0, rn);
             double *d_err = sg.out(errors ? errors + r0 : nullptr, (size_t)rn);
-            if (sg.err != cudaSuccess) return fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
-                                                    "rtb_trace: staging", sg.err);
-            if ((rc = trace_core(ctx, ps, p, a, d_err, errors != nullptr, want_err, false, stride, sg, launches))) return rc;
+            if (sg.err != cudaSuccess)
+                return bail(fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
+                                 "rtb_trace: staging", sg.err));
+            if ((rc = trace_core(ctx, ps, p, a, d_err, errors != nullptr, want_err, false, stride, sg, launches)))
+                return bail(rc);
             sg.copy_back();
         }
-        for (int j = 0; j < 3; ++j) {
-            CK(cudaEventRecord(ctx->pipe_ev[1 + j], ctx->pipe[j]));
-            CK(cudaStreamWaitEvent(st, ctx->pipe_ev[1 + j], 0));
+        cudaError_t je = cudaSuccess;
+        for (int j = 0; j < 3 && je == cudaSuccess; ++j) {
+            je = cudaEventRecord(ctx->pipe_ev[1 + j], ctx->pipe[j]);
+            if (je == cudaSuccess) je = cudaStreamWaitEvent(st, ctx->pipe_ev[1 + j], 0);
         }
-        CK(cudaEventRecord(ctx->ev[2], st));
         unsigned long long total = 0;
-        CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
-        CK(cudaEventRecord(ctx->ev[3], st));
-        CK(cudaStreamSynchronize(st));
+        if (je == cudaSuccess) je = cudaEventRecord(ctx->ev[2], st);
+        if (je == cudaSuccess) je = cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st);
+        if (je == cudaSuccess) je = cudaEventRecord(ctx->ev[3], st);
+        if (je == cudaSuccess) je = cudaStreamSynchronize(st);
+        if (je != cudaSuccess) return bail(fail(ctx, RTB_ERR_CUDA, "rtb_trace: joining the chunk streams", je));
         for (auto &sg : sgs) {
-            if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg.err);
-            h2d += sg.h2d; d2h += sg.d2h;
+            if (sg->err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg->err);
+            h2d += sg->h2d; d2h += sg->d2h;
         }
         if (stats) stats->ray_steps = (int64_t)total;
     } else {
