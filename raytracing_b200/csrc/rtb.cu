@@ -283,7 +283,22 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
     const bool iso = p->gamma == 1.0;
     const bool exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
     const int block = a.lane_shift ? 32 : ctx->block;
-    CK(kLaunch[p->method](a, iso, traj, exact, block, st));
+    const bool two_pass = has_errors && want_err && !(traj && stride == 1);
+    TraceArgs a1 = a;
+    if (two_pass) {
+        // pass 1 leaves the ray state every 2^shift steps so that pass 2 starts near its first sample row instead
+        // of at the ray's origin: at most 32 checkpoints of 136 B per ray, 1 GB in all, else coarser or none
+        int shift = 8;
+        while (((int64_t)a.max_size >> shift) > 32) ++shift;
+        while (shift < 30 && ((int64_t)a.max_size >> shift) * RTB_CKPT_FIELDS * 8 * R > ((int64_t)1 << 30)) ++shift;
+        const int rows = (int)(((int64_t)a.max_size - 1) >> shift);
+        if (rows > 0) {
+            a1.ckpt = (double *)sg.alloc((size_t)rows * RTB_CKPT_FIELDS * 8 * R);
+            if (a1.ckpt) { a1.ckpt_shift = shift; a1.ckpt_rows = rows; }
+            else { (void)cudaGetLastError(); sg.err = cudaSuccess; } // no room: pass 2 integrates from the origin
+        }
+    }
+    CK(kLaunch[p->method](a1, iso, traj, exact, block, st));
     ++launches;
     const unsigned g1 = (unsigned)((R + 127) / 128);
     if (has_errors) {
@@ -299,7 +314,7 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
             double *cap_out = (double *)sg.alloc(sizeof(double) * 4 * R);
             if (!cap_rows || !cap_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_trace: capture buffers", sg.err);
             snell_rows_kernel<<<g1, 128, 0, st>>>(a.d_ray, R, cap_rows);
-            TraceArgs b = a;
+            TraceArgs b = a1;
             b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr;
             b.total_steps = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
             CK(kLaunch[p->method](b, iso, false, exact, block, st));

@@ -38,9 +38,13 @@ struct TraceArgs {
     double *px_stats;          // (3,R) or nullptr
     const int *cap_rows;       // (2,R) rows to capture (pass 2 of the Snell metric) or nullptr
     double *cap_out;           // (4,R): x_a, y_a, x_b, y_b
+    double *ckpt;              // (ckpt_rows, RTB_CKPT_FIELDS, R) or nullptr: ray state after every 2^ckpt_shift steps --
+    int ckpt_shift, ckpt_rows; // written by pass 1 of the Snell metric, read by pass 2 (cap_rows set) to start near row a
     double *exit_out;          // (3,R) or nullptr: point where the last segment crosses the box, travel time there
     unsigned long long *total_steps;
 };
+
+constexpr int RTB_CKPT_FIELDS = 17; // x y ang ux uy n gx gy coef inv_n hn + op7's three past positions
 
 __device__ __forceinline__ void store_row(double *p, int64_t R, double x, double y, double px, double py,
                                           double T, double ang)
@@ -105,6 +109,24 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
     if (EXTRA && cap_a == 0) { capv[0] = s.x; capv[1] = s.y; }
     if (EXTRA && cap_b == 0) { capv[2] = s.x; capv[3] = s.y; }
 
+    // Pass 2 of the Snell metric resumes from the last checkpoint at or before its first captured row: the state
+    // is the one pass 1 had there, the steps that follow are the same instructions on the same values.
+    int i_start = 1;
+    if (EXTRA && !TRAJ && a.ckpt && a.cap_rows) {
+        const int c = min(cap_a >> a.ckpt_shift, a.ckpt_rows);
+        if (c > 0) {
+            const double *q = a.ckpt + ((size_t)(c - 1) * RTB_CKPT_FIELDS) * a.R + rr;
+            s.x = q[0]; s.y = q[a.R]; s.ang = q[2 * a.R]; s.ux = q[3 * a.R]; s.uy = q[4 * a.R]; s.n = q[5 * a.R];
+            s.gx = q[6 * a.R]; s.gy = q[7 * a.R]; s.coef = q[8 * a.R]; s.inv_n = q[9 * a.R]; s.hn = q[10 * a.R];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { hist[k][0] = q[(11 + 2 * k) * a.R]; hist[k][1] = q[(12 + 2 * k) * a.R]; }
+            const int at = c << a.ckpt_shift;
+            if (at == cap_a) { capv[0] = s.x; capv[1] = s.y; }
+            if (at == cap_b) { capv[2] = s.x; capv[3] = s.y; }
+            i_start = at + 1;
+        }
+    }
+
     double *sp = nullptr;
     int next_keep = 0; // next row index that is kept in s_ray
     if (TRAJ) {
@@ -117,9 +139,9 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
     // exit point (two-point shooting search): start of the last segment and the crossing found at exit
     double pvx = s.x, pvy = s.y, pvT = 0.0, ex_t = 1.0;
 
-    bool alive = valid && M > 1;
+    bool alive = valid && i_start < M;
     int last_i = 0;
-    int i = 1;
+    int i = i_start;
     const int Mloop = TRAJ ? a.max_size : M;
     // The loop condition must be warp-uniform (lanes may have different M with per-ray max_sizes):
     // every lane iterates until no lane of the warp is alive; `alive` drops at i+1 >= M.
@@ -181,6 +203,13 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
             if (EXTRA && !TRAJ) {
                 if (i == cap_a) { capv[0] = s.x; capv[1] = s.y; }
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
+                if (a.ckpt && !a.cap_rows && (i & ((1 << a.ckpt_shift) - 1)) == 0 && (i >> a.ckpt_shift) <= a.ckpt_rows) {
+                    double *q = a.ckpt + ((size_t)((i >> a.ckpt_shift) - 1) * RTB_CKPT_FIELDS) * a.R + r;
+                    q[0] = s.x; q[a.R] = s.y; q[2 * a.R] = s.ang; q[3 * a.R] = s.ux; q[4 * a.R] = s.uy; q[5 * a.R] = s.n;
+                    q[6 * a.R] = s.gx; q[7 * a.R] = s.gy; q[8 * a.R] = s.coef; q[9 * a.R] = s.inv_n; q[10 * a.R] = s.hn;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) { q[(11 + 2 * k) * a.R] = hist[k][0]; q[(12 + 2 * k) * a.R] = hist[k][1]; }
+                }
             }
             // boundary test RT:878 (strict)
             const bool outside = !inner && (s.x > a.limx_s || s.x < a.limx_i || s.y > a.limy_s || s.y < a.limy_i);
@@ -269,7 +298,7 @@ template <int METHOD>
 cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
 {
     const unsigned grid = (unsigned)(((a.R << a.lane_shift) + block - 1) / block);
-    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr;
+    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr || a.ckpt != nullptr;
 #define RTB_L(I, T, E)                                                                  \
     do {                                                                                \
         if (extra) trace_kernel<METHOD, I, T, E, true><<<grid, block, 0, st>>>(a);      \
