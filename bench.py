@@ -164,11 +164,17 @@ def run_cuda(args):
     out = dict(d_ray=torch.empty(3, R, dtype=torch.float64, device=dev),
                last_row=torch.empty(6, R, dtype=torch.float64, device=dev))
     gathered = torch.empty(world * 3 * R, dtype=torch.float64, device=dev) if world > 1 else None
+    fused = None
+    if world > 1 and args.gather == "fused":   # d_ray written into every GPU's array by the kernel itself (dist.FusedGather)
+        from raytracing_b200.dist import FusedGather
+        fused = FusedGather(eng, R * world, rank * R)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def one_step():
         r = eng.trace(METHOD, th, x0, y0, step, M, gamma, box, full=False, out=out)
-        if world > 1:  # result gather (NCCL over NVLink), the only collective on the path
+        if fused is not None:  # peers were written by the kernel; ranks only agree that they are done
+            fused.finish()
+        elif world > 1:  # result gather as a separate collective (NCCL over NVLink)
             dist.all_gather_into_tensor(gathered, out["d_ray"].view(-1))
         return r
 
@@ -202,6 +208,13 @@ def run_cuda(args):
         raise RuntimeError("timing events (%.3f ms) do not bracket the kernels (%.3f ms): stream mismatch"
                            % (t_ms, sum(kernel_ms)))
     clocks = sampler.stop() if rank == 0 else None
+    gather_mode = None
+    if world > 1:
+        gather_mode = ("peer stores from the kernel epilogue over NVLink (CUDA IPC) + 1-element all-reduce"
+                       if fused is not None else "NCCL all_gather after the kernel")
+    if fused is not None:   # the remaining legs use the same engine without peers
+        fused.close()
+        fused = None
 
     # end to end through the public host-buffer API: pinned host inputs, H2D + D2H inside the call
     pin = lambda a: torch.from_numpy(a).pin_memory().numpy()
@@ -258,7 +271,8 @@ def run_cuda(args):
                 "config": {"workload": workload_name(world), "scenario": "fisheye", "method": "op6",
                            "rays_per_gpu": R, "max_size": M, "ray_steps_per_step": ray_steps // args.steps,
                            "l2": "flushed (256 MiB write) between timed steps",
-                           "parallelism": "rays sharded x%d, d_ray all_gather" % world if world > 1 else "1 GPU"},
+                           "parallelism": ("rays sharded x%d, d_ray gathered on every GPU: %s" % (world, gather_mode))
+                           if world > 1 else "1 GPU"},
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak / 1e12, "unit": "TFLOP/s",
                              "frac": achieved / (fp64_peak / 1e12),
                              "traffic": NCU_OP6["dram_bytes_per_launch"], "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum; the call's inputs + outputs are 101 MB, mostly absorbed by the 126 MB L2)",
@@ -301,6 +315,8 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-full", action="store_true", help="skip the FULL-trajectory (45.8 GB s_ray) leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
+                    help="N>1: d_ray reaches every GPU by peer stores from the kernel (fused) or by an NCCL all-gather")
     ap.add_argument("--workload", default="fisheye", choices=["fisheye", "vert", "aniso", "shoot"],
                     help="fisheye = the headline configs[1] line (default); vert / aniso / shoot = configs[2..4], "
                          "run by tools/bench_configs.py")

@@ -215,6 +215,24 @@ int rtb_wavefront(rtb_ctx *ctx, int32_t ptr_kind, const double *s_ray, const dou
                   int64_t R, const double *times, int32_t nt, double *out);
 
 /*
+ * Multi-GPU result gather fused into the integration kernel.  The reference is one process that owns every ray's
+ * d_ray (RT:888-890); with the rays sharded over the GPUs of a node (one process per GPU) every rank wants the whole
+ * (3, R_total) array.  Instead of an all-gather after the kernel, each rank's kernel stores a finished ray's column
+ * straight into every peer's array over NVLink (24 B per ray per GPU, hidden behind the stepping):
+ *   rtb_gather_alloc  allocates this rank's (3, R_total) array and returns its 64-byte CUDA IPC handle;
+ *   rtb_gather_open   maps a peer's array from the handle it published (same node);
+ *   rtb_set_gather    world (<= 8) base pointers in rank order -- own array included --, the total ray count and
+ *                     the offset of this rank's fan; world = 0 switches the feature off;
+ *   rtb_gather_close  unmaps (own = 0) or frees (own = 1).
+ * While set, every rtb_trace call with device pointers and a d_ray output also writes the peers.  The arrays are
+ * complete once every rank's call has returned; ranks synchronise among themselves (e.g. a 1-element all-reduce).
+ */
+int rtb_gather_alloc(rtb_ctx *ctx, int64_t bytes, void **ptr, void *handle64);
+int rtb_gather_open(rtb_ctx *ctx, const void *handle64, void **ptr);
+int rtb_gather_close(rtb_ctx *ctx, void *ptr, int32_t own);
+int rtb_set_gather(rtb_ctx *ctx, int32_t world, double *const *bases, int64_t R_total, int64_t offset);
+
+/*
  * Measured FP64 pipe peak (dependent-free DFMA streams on every SM), the roofline denominator
  * of SURVEY.md 8(d); returns FLOP/s (2 per DFMA).
  */

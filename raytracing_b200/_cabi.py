@@ -13,7 +13,8 @@ RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -
 # every symbol include/rtb.h declares
 EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
            "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront",
-           "rtb_fit_field", "rtb_gradient", "rtb_get_field")
+           "rtb_fit_field", "rtb_gradient", "rtb_get_field",
+           "rtb_gather_alloc", "rtb_gather_open", "rtb_gather_close", "rtb_set_gather")
 
 
 class RtbSpline(C.Structure):
@@ -89,5 +90,13 @@ def load():
     lib.rtb_gradient.argtypes = [vp, i32, vp, i64, i64, C.c_double, vp, vp]
     lib.rtb_get_field.restype = C.c_int
     lib.rtb_get_field.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, vp]
+    lib.rtb_gather_alloc.restype = C.c_int
+    lib.rtb_gather_alloc.argtypes = [vp, i64, C.POINTER(vp), vp]
+    lib.rtb_gather_open.restype = C.c_int
+    lib.rtb_gather_open.argtypes = [vp, vp, C.POINTER(vp)]
+    lib.rtb_gather_close.restype = C.c_int
+    lib.rtb_gather_close.argtypes = [vp, vp, i32]
+    lib.rtb_set_gather.restype = C.c_int
+    lib.rtb_set_gather.argtypes = [vp, i32, C.POINTER(vp), i64, i64]
     _lib = lib
     return lib

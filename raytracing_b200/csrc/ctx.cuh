@@ -38,6 +38,10 @@ struct rtb_ctx {
     // host-buffer calls on large fans are cut into chunks whose H2D copy, kernel and D2H copy overlap (rtb_trace)
     cudaStream_t pipe[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // fork + one join per pipe stream
+    // fused result gather (rtb_set_gather): peer base pointers, total rays, this rank's ray offset
+    double *gather[RTB_MAX_PEERS] = {};
+    int gather_world = 0;
+    int64_t gather_R = 0, gather_off = 0;
     std::string err;
     // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
     struct PoolBuf { void *p; size_t bytes; bool used; };

@@ -360,6 +360,11 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     base.limx_i = p->limx_i; base.limx_s = p->limx_s; base.limy_i = p->limy_i; base.limy_s = p->limy_s;
     base.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
     base.total_steps = ctx->d_total;
+    if (ctx->gather_world > 0 && !host && d_ray) {
+        if (ctx->gather_off + R > ctx->gather_R) return fail(ctx, RTB_ERR_ARG, "rtb_trace: fan exceeds the gather window (rtb_set_gather)");
+        for (int pe = 0; pe < ctx->gather_world; ++pe) base.gather[pe] = ctx->gather[pe];
+        base.gather_world = ctx->gather_world; base.gather_R = ctx->gather_R; base.gather_off = ctx->gather_off;
+    }
     base.stage = R >= (1 << 16); // below ~one wave of warps a launch is a latency chain: no staging detour
     int64_t launches = 0, h2d = 0, d2h = 0;
     int rc;
@@ -453,6 +458,58 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
         stats->launches = launches;
         stats->h2d_bytes = h2d; stats->d2h_bytes = d2h;
     }
+    return RTB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Fused multi-GPU result gather: buffers shared between the per-GPU processes of one node through CUDA IPC, written
+// by the integration kernel of every rank (trace_kernel.cuh epilogue).
+// ---------------------------------------------------------------------------------------
+extern "C" int rtb_gather_alloc(rtb_ctx *ctx, int64_t bytes, void **ptr, void *handle64)
+{
+    if (!ctx || !ptr || bytes <= 0) return fail(ctx, RTB_ERR_ARG, "rtb_gather_alloc: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    void *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, (size_t)bytes);
+    if (e != cudaSuccess) return fail(ctx, RTB_ERR_NOMEM, "rtb_gather_alloc", e);
+    if (handle64) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+        e = cudaIpcGetMemHandle((cudaIpcMemHandle_t *)handle64, d);
+        if (e != cudaSuccess) { cudaFree(d); return fail(ctx, RTB_ERR_CUDA, "cudaIpcGetMemHandle", e); }
+    }
+    *ptr = d;
+    return RTB_OK;
+}
+
+extern "C" int rtb_gather_open(rtb_ctx *ctx, const void *handle64, void **ptr)
+{
+    if (!ctx || !handle64 || !ptr) return fail(ctx, RTB_ERR_ARG, "rtb_gather_open: null argument");
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, sizeof(h));
+    CK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RTB_OK;
+}
+
+extern "C" int rtb_gather_close(rtb_ctx *ctx, void *ptr, int32_t own)
+{
+    if (!ctx || !ptr) return RTB_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (own) CK(cudaFree(ptr));
+    else CK(cudaIpcCloseMemHandle(ptr));
+    return RTB_OK;
+}
+
+extern "C" int rtb_set_gather(rtb_ctx *ctx, int32_t world, double *const *bases, int64_t R_total, int64_t offset)
+{
+    if (!ctx) return RTB_ERR_ARG;
+    if (world < 0 || world > RTB_MAX_PEERS) return fail(ctx, RTB_ERR_ARG, "rtb_set_gather: world must be 0..8");
+    if (world > 0 && (!bases || R_total <= 0 || offset < 0 || offset >= R_total))
+        return fail(ctx, RTB_ERR_ARG, "rtb_set_gather: bad window");
+    for (int pe = 0; pe < world; ++pe)
+        if (!bases[pe]) return fail(ctx, RTB_ERR_ARG, "rtb_set_gather: null peer buffer");
+    for (int pe = 0; pe < RTB_MAX_PEERS; ++pe) ctx->gather[pe] = pe < world ? bases[pe] : nullptr;
+    ctx->gather_world = world; ctx->gather_R = R_total; ctx->gather_off = offset;
     return RTB_OK;
 }
 

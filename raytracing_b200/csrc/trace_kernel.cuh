@@ -17,6 +17,8 @@ namespace rtb {
 #define RTB_BLOCK 128
 #endif
 
+#define RTB_MAX_PEERS 8
+
 struct TraceArgs {
     DevField f;
     const DevField *f_dev;     // the same struct in global memory (rare out-of-line paths)
@@ -42,6 +44,11 @@ struct TraceArgs {
     int ckpt_shift, ckpt_rows; // written by pass 1 of the Snell metric, read by pass 2 (cap_rows set) to start near row a
     double *exit_out;          // (3,R) or nullptr: point where the last segment crosses the box, travel time there
     unsigned long long *total_steps;
+    // Multi-GPU result gather fused into the kernel (rtb_set_gather): every finished ray also stores its d_ray column
+    // into the (3, gather_R) array of each peer GPU, at ray offset gather_off, over NVLink peer mappings.
+    double *gather[RTB_MAX_PEERS];
+    int gather_world;
+    int64_t gather_R, gather_off;
 };
 
 constexpr int RTB_CKPT_FIELDS = 17; // x y ang ux uy n gx gy coef inv_n hn + op7's three past positions
@@ -255,6 +262,12 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
             a.d_ray[r] = dist_real;
             a.d_ray[a.R + r] = dist_sim;
             a.d_ray[2 * a.R + r] = (double)last_i;
+            for (int pe = 0; pe < a.gather_world; ++pe) { // peer stores: 24 B per ray per GPU, hidden behind the stepping
+                double *g = a.gather[pe] + a.gather_off + r;
+                g[0] = dist_real;
+                g[a.gather_R] = dist_sim;
+                g[2 * a.gather_R] = (double)last_i;
+            }
         }
         if (a.last_row) {
             a.last_row[r] = s.x; a.last_row[a.R + r] = s.y;

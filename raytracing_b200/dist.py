@@ -39,6 +39,60 @@ def gather_rays(local, R, group=None):
     return torch.cat([b[..., :n] for b, n in zip(bufs, sizes)], dim=-1)
 
 
+class _DevArray:
+    """A (3, R) float64 device buffer owned by librtb, exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, R):
+        self.__cuda_array_interface__ = dict(shape=(3, int(R)), typestr="<f8", data=(int(ptr), False), version=3,
+                                             strides=None)
+
+
+class FusedGather:
+    """Result gather fused into the integration kernel: every rank's trace kernel stores a finished
+    ray's d_ray column straight into the (3, R_total) array of every GPU of the node over NVLink peer mappings
+    (CUDA IPC between the per-GPU processes), so no all-gather follows the kernel -- ranks only agree that they are
+    done (`finish`: a one-element all-reduce).  Same bytes as `gather_rays(d_ray)`.
+
+        fg = FusedGather(engine, R_total, lo, group)      # collective: exchanges IPC handles
+        engine.trace(...device tensors of rays lo..hi...) # writes every peer
+        d_ray_all = fg.finish()                           # torch view (3, R_total) of this rank's copy
+        fg.close()                                        # collective
+    """
+
+    def __init__(self, engine, R_total, offset, group=None):
+        import torch
+        import torch.distributed as dist
+        self.engine, self.group, self.R = engine, group, int(R_total)
+        engine.use_torch_stream()      # the kernels and the finishing all-reduce must be ordered on one stream
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > 8:
+            raise ValueError("FusedGather: at most 8 GPUs (one node)")
+        self.own, handle = engine.gather_alloc(3 * 8 * self.R)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle, group=group)
+        self.bases = [self.own if r == self.rank else engine.gather_open(handles[r]) for r in range(self.world)]
+        engine.set_gather(self.bases, self.R, offset)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", engine.device))
+        self.view = torch.as_tensor(_DevArray(self.own, self.R), device=self._flag.device)
+        dist.barrier(group=group)      # every peer has mapped this buffer before anyone traces
+
+    def finish(self):
+        """All ranks' kernels have completed (stream-ordered after this rank's own): the local array is whole."""
+        import torch.distributed as dist
+        dist.all_reduce(self._flag, group=self.group)
+        return self.view
+
+    def close(self):
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize(self.engine.device)
+        self.engine.set_gather(None, 0, 0)
+        dist.barrier(group=self.group)  # nobody is still writing into a buffer about to be unmapped / freed
+        for r, b in enumerate(self.bases):
+            self.engine.gather_close(b, own=(r == self.rank))
+        self.bases = []
+
+
 def reduce_sum_max(sum_vals, max_vals, group=None):
     """All-reduce per-candidate partial sums (SUM) and maxima (MAX) in place; used for the mean/max
     Snell error of a sweep whose rays span ranks (RT_bench.py:954)."""

@@ -186,6 +186,28 @@ class Engine:
                                             c.ctypes.data))
         return tu, tv, c
 
+    # -- fused multi-GPU result gather (include/rtb.h rtb_gather_*, rtb_set_gather) --
+    def gather_alloc(self, nbytes):
+        """(device pointer, 64-byte IPC handle) of a new buffer on this GPU that peers can map."""
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        self._check(self._lib.rtb_gather_alloc(self._ctx, int(nbytes), C.byref(ptr), handle))
+        return ptr.value, handle.raw
+
+    def gather_open(self, handle):
+        ptr = C.c_void_p()
+        self._check(self._lib.rtb_gather_open(self._ctx, C.create_string_buffer(bytes(handle), 64), C.byref(ptr)))
+        return ptr.value
+
+    def gather_close(self, ptr, own):
+        self._check(self._lib.rtb_gather_close(self._ctx, C.c_void_p(ptr), 1 if own else 0))
+
+    def set_gather(self, bases, R_total, offset):
+        """While set, device-pointer traces also store d_ray into every buffer of `bases` (rank order, own
+        included) at ray offset `offset` of a (3, R_total) array.  set_gather(None, 0, 0) switches it off."""
+        n = len(bases) if bases else 0
+        arr = (C.c_void_p * max(n, 1))(*[C.c_void_p(b) for b in (bases or [])])
+        self._check(self._lib.rtb_set_gather(self._ctx, n, arr, int(R_total), int(offset)))
+
     def fp64_peak(self):
         v = C.c_double()
         self._check(self._lib.rtb_fp64_peak(self._ctx, C.byref(v)))

@@ -1,4 +1,5 @@
 """GPU parity tests: the CUDA path through the C ABI vs the oracle and the golden fixtures."""
+import os
 import numpy as np
 import pytest
 
@@ -166,3 +167,58 @@ def test_warp_staged_records_equal_per_lane_loads(engine, uc, m):
     for name in ("d_ray", "last_row"):
         assert np.array_equal(np.concatenate([h[name] for h in halves], 1), whole[name], equal_nan=True), name
     assert np.array_equal(np.concatenate([h.s_ray for h in halves], 2), whole.s_ray, equal_nan=True)
+
+
+def test_fused_gather_two_contexts_one_gpu():
+    """rtb_set_gather: the kernel epilogue of every 'rank' stores its d_ray columns into every gather array.  Two
+    contexts on one GPU stand in for two ranks (the IPC mapping itself is covered by tests/mgpu_fused_gather.py)."""
+    import torch
+    import raytracing_b200 as rt
+    from raytracing_b200.dist import _DevArray, shard_bounds
+    from raytracing_b200 import _cabi
+    s = scenario_setup("3")
+    R = 5000
+    dev = torch.device("cuda", 0)
+    th, x0, y0 = rt.make_fan("3", R)
+    eng = [rt.Engine(0), rt.Engine(0)]
+    bufs = [e.gather_alloc(3 * 8 * R)[0] for e in eng]
+    views = [torch.as_tensor(_DevArray(b, R), device=dev) for b in bufs]
+    for v in views:
+        v.fill_(-7.0)
+    parts = []
+    for rank, e in enumerate(eng):
+        e.set_field(s["z"], s["grd"])
+        lo, hi = shard_bounds(R, 2, rank)
+        e.set_gather(bufs, R, lo)
+        parts.append(e.trace(6, *(torch.from_numpy(a[lo:hi]).to(dev) for a in (th, x0, y0)), s["step"], s["M"],
+                             s["gamma"], s["box"], full=False))
+    torch.cuda.synchronize()
+    whole = torch.cat([p.d_ray for p in parts], 1)
+    assert torch.equal(views[0], whole) and torch.equal(views[1], whole)
+    with pytest.raises(_cabi.RtbError):            # a fan that does not fit the window is refused
+        eng[1].trace(6, *(torch.from_numpy(a).to(dev) for a in (th, x0, y0)), s["step"], s["M"], s["gamma"], s["box"],
+                     full=False)
+    eng[0].set_gather(None, 0, 0)                  # off again: the arrays are no longer touched
+    views[0].fill_(-7.0)
+    eng[0].trace(6, *(torch.from_numpy(a[:100]).to(dev) for a in (th, x0, y0)), s["step"], s["M"], s["gamma"], s["box"],
+                 full=False)
+    torch.cuda.synchronize()
+    assert bool((views[0] == -7.0).all())
+    for e, b in zip(eng, bufs):
+        e.set_gather(None, 0, 0)
+        e.gather_close(b, own=True)
+        e.close()
+
+
+def test_fused_gather_across_processes():
+    """Two processes, two GPUs, CUDA IPC peer mappings (skipped on a one-GPU box)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29577", os.path.join(here, "mgpu_fused_gather.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "fused gather ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
