@@ -167,7 +167,11 @@ def run_cuda(args):
     fused = None
     if world > 1 and args.gather == "fused":   # d_ray written into every GPU's array by the kernel itself (dist.FusedGather)
         from raytracing_b200.dist import FusedGather
-        fused = FusedGather(eng, R * world, rank * R)
+        try:
+            fused = FusedGather(eng, R * world, rank * R)
+        except RuntimeError as e:   # raised on every rank alike: fall back to the NCCL all-gather
+            if rank == 0:
+                print("bench: fused gather unavailable (%s), using NCCL all_gather" % e, file=sys.stderr)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def one_step():

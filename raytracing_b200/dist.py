@@ -67,14 +67,35 @@ class FusedGather:
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         if self.world > 8:
             raise ValueError("FusedGather: at most 8 GPUs (one node)")
-        self.own, handle = engine.gather_alloc(3 * 8 * self.R)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", engine.device))
+        self.own, self.bases, err = None, [], None
+        try:
+            self.own, handle = engine.gather_alloc(3 * 8 * self.R)
+        except Exception as e:  # the outcome is agreed on below: no rank may leave the others in a collective
+            handle, err = None, e
         handles = [None] * self.world
         dist.all_gather_object(handles, handle, group=group)
-        self.bases = [self.own if r == self.rank else engine.gather_open(handles[r]) for r in range(self.world)]
+        if err is None and all(h is not None for h in handles):
+            try:
+                self.bases = [self.own if r == self.rank else engine.gather_open(handles[r]) for r in range(self.world)]
+            except Exception as e:
+                err = e
+        ok = torch.tensor([0 if err is not None or not self.bases else 1], dtype=torch.int32, device=self._flag.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 0:     # some rank could not allocate / map (no peer access): nobody uses the fused path
+            self._release()
+            raise RuntimeError("FusedGather: peer mapping unavailable on at least one rank (%s)" % (err,))
         engine.set_gather(self.bases, self.R, offset)
-        self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", engine.device))
         self.view = torch.as_tensor(_DevArray(self.own, self.R), device=self._flag.device)
         dist.barrier(group=group)      # every peer has mapped this buffer before anyone traces
+
+    def _release(self):
+        for r, b in enumerate(self.bases):
+            if r != self.rank:
+                self.engine.gather_close(b, own=False)
+        if self.own is not None:
+            self.engine.gather_close(self.own, own=True)
+        self.bases, self.own = [], None
 
     def finish(self):
         """All ranks' kernels have completed (stream-ordered after this rank's own): the local array is whole."""
@@ -88,9 +109,7 @@ class FusedGather:
         torch.cuda.synchronize(self.engine.device)
         self.engine.set_gather(None, 0, 0)
         dist.barrier(group=self.group)  # nobody is still writing into a buffer about to be unmapped / freed
-        for r, b in enumerate(self.bases):
-            self.engine.gather_close(b, own=(r == self.rank))
-        self.bases = []
+        self._release()
 
 
 def reduce_sum_max(sum_vals, max_vals, group=None):
