@@ -135,6 +135,56 @@ __device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_les
     return th;
 }
 
+// golden (RT:175-199) for the isotropic cost without evaluating it: f(t) = |n1 (cos t, sin t) - A|^2 =
+// n1^2 + |A|^2 - 2 n1 |A| cos(t - ts) is symmetric about ts = arg A, so f(c) < f(d) <=> the midpoint of the probes
+// lies right of ts.  The bracket arithmetic (a, b, c, d, the loop test, the result (a+b)/2) is the reference's own;
+// each decision costs one addition and one comparison against ts = theta + delta, delta from the cross and dot
+// products of A with the ray direction.  Where the reference's computed f(c) - f(d) would be within its own rounding
+// noise -- |2 mu|^2 <= TIE^2 (D^2 / (|A|^2 q^2) + n1 / |A|), mu = midpoint - ts, q = half the probe distance (a
+// constant per iteration), D = n1 - |A|: the same criterion as golden_trig's, in the angle domain, taken twice as
+// wide -- both probes are evaluated like the reference does (exact_less).  Returns false when ts is more than 2^-6
+// from theta (a turn no step of the tested scenarios makes): the caller then runs golden_trig.
+template <class FX>
+__device__ __forceinline__ bool golden_iso_sym(double n1, double ax, double ay, const FX &exact_less, double theta,
+                                               double st, double ct, double &th_out, double &s_out, double &c_out)
+{
+    const double A2 = fma(ax, ax, ay * ay);
+    const double rA = rsqrt_fast3(A2);
+    const double cs = ax * rA, ss = ay * rA;     // (cos, sin)(ts)
+    const double sd = fma(ct, ss, -(st * cs));   // sin(ts - theta)
+    const double cd = fma(ct, cs, st * ss);      // cos(ts - theta)
+    if (!(cd > 0.99988)) return false;           // |ts - theta| < 2^-6 (cos 2^-6 = 0.999877933)
+    const double t = sd * rcp_fast3(cd), t2 = t * t;
+    double p = fma(t2, 1.0 / 9.0, -1.0 / 7.0);   // atan t = t - t^3/3 + t^5/5 - t^7/7 + t^9/9, |t| < 2^-6
+    p = fma(p, t2, 0.2);
+    p = fma(p, t2, -1.0 / 3.0);
+    const double delta = fma(t * t2, p, t), delta2 = 2.0 * delta;
+    const double D = fma(-A2, rA, n1);
+    const double K = RTB_TIE_EPS * RTB_TIE_EPS;
+    const double alpha = K * (D * rA) * (D * rA), beta = K * n1 * rA;
+    double a = theta - RTB_DELTA_G, b = theta + RTB_DELTA_G;
+    double c = b - (b - a) * RTB_GOLD_RATIO;
+    double d = a + (b - a) * RTB_GOLD_RATIO;
+    int k = 0;
+#pragma unroll 1
+    while (fabs(c - d) > RTB_GOLD_TOL) {
+        const double M = ((c - theta) + (d - theta)) - delta2; // 2 (midpoint - ts)
+        bool left = M > 0.0;                                   // RT:189: if func(c) < func(d): b = d  else: a = c
+        if (M * M <= fma(alpha, kGoldenInvQ2[min(k, RTB_GOLDEN_ROT_N - 1)], beta)) left = exact_less(c, d);
+        b = left ? d : b;
+        a = left ? a : c;
+        c = b - (b - a) * RTB_GOLD_RATIO;
+        d = a + (b - a) * RTB_GOLD_RATIO;
+        ++k;
+    }
+    const double th = (b + a) / 2.0;
+    const double e = (th - theta) - delta, e2h = 0.5 * e * e; // |e| <= final bracket ~3e-8
+    s_out = fma(-ss, e2h, fma(cs, e, ss));
+    c_out = fma(-cs, e2h, fma(-ss, e, cs));
+    th_out = th;
+    return true;
+}
+
 // One step.  Updates the state in place; returns dist = |r1 - r0|.  LAZY: theta of atan2-type
 // updaters is not evaluated (s.ang stale); `i` is the step index (resync schedule).
 template <int METHOD, bool ISO, bool LAZY>
@@ -270,8 +320,12 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
             sincos_cw_inline(pd, s2, c2);
             return cf(s1, c1) < cf(s2, c2);
         };
-        double ns, nc;
-        s.ang = golden_trig(cf, exact_less, fn, s.ang, s.uy, s.ux, ns, nc);
+        double ns, nc, th;
+#ifndef RTB_NO_GOLDEN_SYM
+        if (!golden_iso_sym(fn, cf.ax, cf.ay, exact_less, s.ang, s.uy, s.ux, th, ns, nc))
+#endif
+            th = golden_trig(cf, exact_less, fn, s.ang, s.uy, s.ux, ns, nc);
+        s.ang = th;
         if ((i & RTB_RESYNC_MASK) == 0) sincos_cw(s.ang, ns, nc); // periodic exact resync of the carried (sin, cos)
         s.uy = ns; s.ux = nc;
     } else { // golden, anisotropic cost RT:728,761
