@@ -49,16 +49,17 @@ struct CostAnisoFast {
     double n1, gamma, g2m1, mx, my, gx1h, gy1h; // mx = mi_x + h*coef_i*gx0/2 ; gx1h = h*gx1/2
     __device__ __forceinline__ double operator()(double s, double c) const
     {
-        const double gs = gamma * s, s2 = s * s, c2 = c * c;
-        const double v = fma(gs, gs, c2); // anisotropy^2, in [1, gamma^2]
-        double y;                         // 1/sqrt(v): MUFU seed + one cubically convergent step
+        // anisotropy^2 = gamma^2 s^2 + c^2 = 1 + (gamma^2 - 1) s^2 =: v, coef = sqrt(v) = v y with y = 1/sqrt(v), and
+        // coef (1 - s^2 k) = coef - w s^2, coef (1 + c^2 k) = coef + w c^2 with k = (gamma^2 - 1)/v, w = (gamma^2 - 1) y
+        const double s2 = s * s, c2 = c * c;
+        const double v = fma(g2m1, s2, 1.0);
+        double y; // MUFU seed + one cubically convergent step
         asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
         const double e = fma(-v * y, y, 1.0);
         y = fma(y, fma(e, 0.375, 0.5) * e, y);
-        const double coef = v * y, k = g2m1 * (y * y);
-        const double nc = n1 * coef;
-        const double a = fma(nc * c, fma(-s2, k, 1.0), -fma(coef, gx1h, mx));
-        const double b = fma(nc * s, fma(c2, k, 1.0), -fma(coef, gy1h, my));
+        const double coef = v * y, w = g2m1 * y;
+        const double a = fma(n1 * c, fma(-w, s2, coef), -fma(coef, gx1h, mx));
+        const double b = fma(n1 * s, fma(w, c2, coef), -fma(coef, gy1h, my));
         return fma(a, a, b * b);
     }
 };
