@@ -66,9 +66,10 @@ __device__ __forceinline__ void store_row(double *p, int64_t R, double x, double
 
 // EXACT = faithful restatement (reference evaluation order, libdevice sincos, IEEE div/sqrt, FITPACK
 // recurrence): the parity anchor.  !EXACT = default B200 form (step_fast.cuh).
-// EXTRA = p_x statistics and/or Snell row capture requested (kept out of the plain kernels: their
-// accumulators cost 15 registers).
-template <int METHOD, bool ISO, bool TRAJ, bool EXACT, bool EXTRA>
+// EXTRA = 1: p_x statistics, Snell row capture or exit points requested (kept out of the plain kernels: their
+// accumulators cost 15 registers); EXTRA = 2: the same plus saving / resuming from ray-state checkpoints (the two
+// passes of the Snell metric; its own flavour because the checkpoint code costs the others 130 B of spills).
+template <int METHOD, bool ISO, bool TRAJ, bool EXACT, int EXTRA>
 __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB_MIN_BLOCKS) trace_kernel(const TraceArgs a)
 {
     constexpr int UPD = updater_of(METHOD);
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
     // Pass 2 of the Snell metric resumes from the last checkpoint at or before its first captured row: the state
     // is the one pass 1 had there, the steps that follow are the same instructions on the same values.
     int i_start = 1;
-    if (EXTRA && !TRAJ && a.ckpt && a.cap_rows) {
+    if (EXTRA == 2 && !TRAJ && a.ckpt && a.cap_rows) {
         const int c = min(cap_a >> a.ckpt_shift, a.ckpt_rows);
         if (c > 0) {
             const double *q = a.ckpt + ((size_t)(c - 1) * RTB_CKPT_FIELDS) * a.R + rr;
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
             if (EXTRA && !TRAJ) {
                 if (i == cap_a) { capv[0] = s.x; capv[1] = s.y; }
                 if (i == cap_b) { capv[2] = s.x; capv[3] = s.y; }
-                if (a.ckpt && !a.cap_rows && (i & ((1 << a.ckpt_shift) - 1)) == 0 && (i >> a.ckpt_shift) <= a.ckpt_rows) {
+                if (EXTRA == 2 && a.ckpt && !a.cap_rows && (i & ((1 << a.ckpt_shift) - 1)) == 0 && (i >> a.ckpt_shift) <= a.ckpt_rows) {
                     double *q = a.ckpt + ((size_t)((i >> a.ckpt_shift) - 1) * RTB_CKPT_FIELDS) * a.R + r;
                     q[0] = s.x; q[a.R] = s.y; q[2 * a.R] = s.ang; q[3 * a.R] = s.ux; q[4 * a.R] = s.uy; q[5 * a.R] = s.n;
                     q[6 * a.R] = s.gx; q[7 * a.R] = s.gy; q[8 * a.R] = s.coef; q[9 * a.R] = s.inv_n; q[10 * a.R] = s.hn;
@@ -311,11 +312,13 @@ template <int METHOD>
 cudaError_t launch_trace(const TraceArgs &a, bool iso, bool traj, bool exact, int block, cudaStream_t st)
 {
     const unsigned grid = (unsigned)(((a.R << a.lane_shift) + block - 1) / block);
-    const bool extra = a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr || a.ckpt != nullptr;
+    const int extra = (a.ckpt != nullptr && !traj) ? 2
+                    : (a.px_stats != nullptr || a.cap_rows != nullptr || a.exit_out != nullptr) ? 1 : 0;
 #define RTB_L(I, T, E)                                                                  \
     do {                                                                                \
-        if (extra) trace_kernel<METHOD, I, T, E, true><<<grid, block, 0, st>>>(a);      \
-        else trace_kernel<METHOD, I, T, E, false><<<grid, block, 0, st>>>(a);           \
+        if (extra == 2) trace_kernel<METHOD, I, false, E, 2><<<grid, block, 0, st>>>(a); \
+        else if (extra) trace_kernel<METHOD, I, T, E, 1><<<grid, block, 0, st>>>(a);    \
+        else trace_kernel<METHOD, I, T, E, 0><<<grid, block, 0, st>>>(a);               \
     } while (0)
     if (iso) {
         if (traj) { if (exact) RTB_L(true, true, true); else RTB_L(true, true, false); }
