@@ -32,7 +32,7 @@ RAYS_PER_GPU = 1 << 20
 # 25 flop per sin or cos) is larger than what the kernel executes, so `roofline.frac` can exceed 1; the executed
 # figures below are the hardware-side view of the same launch.
 NCU_OP6 = {"dfma": 59.5, "dmul": 19.4, "dadd": 13.3, "l1_data_pipe_frac": 0.59, "fp64_pipe_active_frac": 0.637,
-           "dram_bytes_per_launch": 26.645e6 + 19.594e6, "source": "profiles/r1h_ncu_full_op6_fisheye1M.csv"}
+           "dram_bytes_per_launch": 26.645e6 + 19.594e6, "source": "profiles/r1j_ncu_full_op6_fisheye1M.csv"}
 METRIC = "fp64_ray_steps_per_s"
 UNIT = "ray-steps/s"
 
