@@ -222,3 +222,25 @@ def test_fused_gather_across_processes():
                         "--master-addr", "127.0.0.1", "--master-port", "29577", os.path.join(here, "mgpu_fused_gather.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "fused gather ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("uc,m,div", [("3", 9, 2.74), ("3", 5, 2.53), ("2", 9, 325), ("3", 6, 2.55), ("3", 3, 2.34),
+                                      ("3", 9, 1.0), ("3", 6, 0.6)])
+def test_coarse_steps_vs_oracle(engine, uc, m, div):
+    """The reference's calibrated DELTA_S (RT:1413-1455) are 7-8x the default step, and the coarse end of its sweeps
+    larger still: per-step turns leave the small-angle forms of step_fast.cuh (the midpoint golden search hands over to
+    the evaluating one beyond 2^-6, the rotations and the step-length series to their general branches).  Same parity
+    bar against the CPU restatement as for the default step."""
+    import raytracing_b200 as rt
+    s = scenario_setup(uc)
+    engine.set_field(s["z"], s["grd"])
+    if uc == "2":
+        step, M = 2 * np.pi / div, rt.max_size_for(uc, 2 * np.pi / div, int(div) + 1)
+    else:
+        step = rt.SIGMA / div
+        M = rt.max_size_for(uc, step, rt.DELTA_S_DIVISOR_FISHEYE + 1)
+    r = engine.trace(m, s["theta0"], s["x0"], s["y0"], step, M, s["gamma"], s["box"], full=True)
+    o = _oracle(s, uc, m, step=step, M=M)
+    assert np.array_equal(r.d_ray[2], o["d_ray"][2])
+    assert_close(r.s_ray, o["s_ray"], 1e-10, "s_ray")
+    assert_close(r.d_ray[:2], o["d_ray"][:2], 1e-10, "d_ray")
