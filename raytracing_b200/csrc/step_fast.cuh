@@ -212,11 +212,22 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         fy = fma(s.ux, w, fma(s.uy, h, s.y));
         if (UPD != 2 || bootstrap) dist = sqrt_pos(fma(w, w, h * h)); // UPD == 2 takes it from k1^2 below
     } else {
+        // curvature_t RT:342-365: the arc of radius R = n / cross through the turn e = k1.  Written without the
+        // radius: R (sin(t+e) - sin t) = h (ux sin(e)/e + uy (cos e - 1)/e), so the reference's cancelling difference,
+        // its division by the curvature and the square root of the chord (2 R sin(e/2) = h (1 - e^2/24 + e^4/1920))
+        // all become short even/odd series in e for |e| < 2^-8; larger turns take the literal form below.
         const double curv = fabs(cross) * s.inv_n;
-        if (curv < RTB_GOLD_TOL) {
-            fx = fma(s.ux, h, s.x);
-            fy = fma(s.uy, h, s.y);
-            ignore = false;
+        const bool straight = curv < RTB_GOLD_TOL; // RT:349: first-order step, angle left alone
+        if (straight) ignore = false;
+        if (abs_lt_hi(k1, HI_2M8)) {
+            const double z = k1 * k1;
+            const double S = fma(z, fma(z, K_1_120, -K_SIXTH), 1.0); // sin(e)/e
+            const double eC = k1 * fma(z, K_1_24, -0.5);               // (cos e - 1)/e
+            double tx = fma(s.uy, eC, s.ux * S), ty = fma(-s.ux, eC, s.uy * S);
+            if (straight) { tx = s.ux; ty = s.uy; }
+            fx = fma(h, tx, s.x);
+            fy = fma(h, ty, s.y);
+            dist = straight ? h : h * fma(z, fma(z, 1.0 / 1920.0, -1.0 / 24.0), 1.0);
         } else {
             const double d = curv * h;
             const double sg = (cross < 0) ? -1.0 : 1.0; // RT:360: -1 where gx*uy - gy*ux > 0
@@ -237,9 +248,9 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
             const double icurv = s.n * rcp_fast(cross); // signed radius: sg / curvature
             fx = fma(ds, icurv, s.x);
             fy = fma(-dc, icurv, s.y);
+            const double dx = s.x - fx, dy = s.y - fy;
+            dist = sqrt_pos(fma(dx, dx, dy * dy));
         }
-        const double dx = s.x - fx, dy = s.y - fy;
-        dist = sqrt_pos(fma(dx, dx, dy * dy));
     }
     double fn, fgx, fgy;
     inner = n_gradient_cells(f, fd, in, fx, fy, fn, fgx, fgy, mask, wbuf); // true: new position strictly inside the box
