@@ -210,7 +210,10 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         const double w = (0.5 * h) * k1;
         fx = fma(-s.uy, w, fma(s.ux, h, s.x));
         fy = fma(s.ux, w, fma(s.uy, h, s.y));
-        if (UPD != 2 || bootstrap) dist = sqrt_pos(fma(w, w, h * h)); // UPD == 2 takes it from k1^2 below
+        if (UPD != 2 || bootstrap) { // UPD == 2 takes it from the k1^2 of its rotation below
+            const double z = k1 * k1;  // |dx| = h sqrt(1 + (k1/2)^2) = h (1 + z/8 - z^2/128 + O(z^3 2^-10)), z < 2^-16
+            dist = abs_lt_hi(k1, HI_2M8) ? fma(h, z * fma(z, -0.0078125, 0.125), h) : sqrt_pos(fma(w, w, h * h));
+        }
     } else {
         // curvature_t RT:342-365: the arc of radius R = n / cross through the turn e = k1.  Written without the
         // radius: R (sin(t+e) - sin t) = h (ux sin(e)/e + uy (cos e - 1)/e), so the reference's cancelling difference,
