@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RTB_ABI_VERSION 1
+#define RTB_ABI_VERSION 2
 
 typedef struct rtb_ctx rtb_ctx;
 
@@ -67,6 +67,10 @@ typedef struct {
 #define RTB_F_NO_TAIL_ZERO 4u /* s_ray was zero-filled by the caller: do not write the rows after a ray's
                                  last step (np.zeros, RT:802) */
 
+#define RTB_F_STATIC_GRID 8u  /* one thread per ray for the whole launch (the only mapping for trajectories).  Default for
+                                 FINAL-type outputs of fans >= 2^16 rays: persistent warps pull rays from a queue and
+                                 compact when lanes finish (warp ballot + refill); results are bit-identical either way */
+
 typedef struct {
     int32_t method;     /* 1..11 = op1..op11 (RT:469-764); the shim maps function objects to ids  */
     uint32_t flags;     /* RTB_F_*                                                                  */
@@ -90,6 +94,9 @@ typedef struct {
     int64_t ray_steps;  /* sum over rays of d_ray[2] = executions of the loop body RT:867-879      */
     int64_t launches;   /* kernels launched by the call                                            */
     int64_t h2d_bytes, d2h_bytes; /* staged bytes (RTB_PTR_HOST)                                   */
+    int64_t nonfinite_rays; /* rays whose last position or travel time is NaN/Inf.  Like the reference (whose box
+                               tests are all false for NaN, RT:878) such a ray is stepped on to max_size; this is
+                               the guard flag that tells the caller it happened                               */
 } rtb_stats;
 
 /* Create / destroy the per-GPU context (replaces the reference's process-global state). */
@@ -100,6 +107,15 @@ void rtb_destroy(rtb_ctx *ctx);
 int rtb_set_stream(rtb_ctx *ctx, void *cuda_stream);
 const char *rtb_last_error(rtb_ctx *ctx);
 int rtb_abi_version(void);
+/* Hex digest of the CUDA sources the library was compiled from (written by csrc/Makefile): lets a caller check that a
+   prebuilt librtb.so matches the source tree it sits in. */
+const char *rtb_build_id(void);
+/* Tuning / test switches of a context.  RTB_OPT_QUEUE: 0 = auto (ray queue for FINAL-type outputs of large fans),
+   1 = always where possible, 2 = never (static grid).  RTB_OPT_TRAJ_STORE: 0 = auto (trajectory rows leave through
+   shared memory as 256-byte bulk copies when R is even), 1 = per-lane st.global. */
+#define RTB_OPT_QUEUE 1
+#define RTB_OPT_TRAJ_STORE 2
+int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value);
 
 /*
  * Upload the field: z = bilinear spline of n, gu = grd[0] (d n/d y), gv = grd[1] (d n/d x),
@@ -153,6 +169,33 @@ int rtb_field_eval(rtb_ctx *ctx, int32_t ptr_kind, uint32_t flags, const double 
 int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0,
               const double *y0, int64_t R, double *s_ray, double *d_ray, double *errors,
               double *last_row, double *px_stats, rtb_stats *stats);
+
+/*
+ * The DELTA_S sweep (RT:1303-1318: executor.map(search_delta, ...) over the candidate steps) as ONE batched trace of
+ * C candidates x R rays with the per-candidate reductions done on the device, so a C caller gets what the selection
+ * rules (find_index RT:1323-1373) consume without copying per-ray data:
+ *   RTB_SWEEP_SNELL   (interface): m[c][k] = Snell error of ray k (RT:896-919);   mean = sum/count, max (RT:954)
+ *   RTB_SWEEP_CLOSURE (fisheye)  : m[c]    = 100 |(1,0) - rays[-1, 0:2, 0]| / 2pi of the fan's FIRST ray (RT:956;
+ *                                  rays[-1] is row max_size-1, zero if the ray ended earlier); count 1
+ *   RTB_SWEEP_PX_CV   (vert/aniso): m[c][k] = 100 std/mean of the non-zero p_x entries of ray k (RT:1358-1359) over
+ *                                  rays skip_lo <= k < R - skip_hi (the reference leaves out its first and last ray)
+ * theta0/x0/y0 (R) is the fan every candidate traces; steps/max_sizes (C) the candidates.  Outputs (C each; host or
+ * device per p->ptr_kind): sum[c], max[c], count[c].  The reductions use a fixed tree (bitwise reproducible); a fan
+ * sharded over several GPUs all-reduces sum/count (SUM) and max (MAX).  p->step, p->max_size, p->steps, p->max_sizes
+ * are ignored; p->method/flags/gamma/box as in rtb_trace.
+ */
+#define RTB_SWEEP_SNELL 1
+#define RTB_SWEEP_CLOSURE 2
+#define RTB_SWEEP_PX_CV 3
+typedef struct {
+    const double *steps;      /* (C) DELTA_S candidates                        */
+    const int64_t *max_sizes; /* (C) rows per candidate (RT:796-799)            */
+    int64_t C;
+    int32_t metric;           /* RTB_SWEEP_*                                    */
+    int64_t skip_lo, skip_hi; /* RTB_SWEEP_PX_CV: local rays left out at both ends */
+} rtb_sweep_spec;
+int rtb_sweep(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0, const double *y0, int64_t R,
+              const rtb_sweep_spec *spec, double *sum, double *max, int64_t *count, rtb_stats *stats);
 
 /*
  * Batched two-point shooting search (BASELINE.json configs[4]).  The reference has NO two-point
@@ -224,13 +267,19 @@ int rtb_wavefront(rtb_ctx *ctx, int32_t ptr_kind, const double *s_ray, const dou
  *   rtb_set_gather    world (<= 8) base pointers in rank order -- own array included --, the total ray count and
  *                     the offset of this rank's fan; world = 0 switches the feature off;
  *   rtb_gather_close  unmaps (own = 0) or frees (own = 1).
- * While set, every rtb_trace call with device pointers and a d_ray output also writes the peers.  The arrays are
- * complete once every rank's call has returned; ranks synchronise among themselves (e.g. a 1-element all-reduce).
+ * While set, every rtb_trace call with DEVICE pointers and a d_ray output also writes the peers (calls with host
+ * pointers do not: their results go back to the host).  The arrays are complete once every rank's call has returned;
+ * ranks synchronise among themselves (e.g. a 1-element all-reduce).  A consumer that reads its array while peers may
+ * already run their NEXT trace must alternate between two sets of arrays (raytracing_b200.dist.FusedGather does).
  */
 int rtb_gather_alloc(rtb_ctx *ctx, int64_t bytes, void **ptr, void *handle64);
 int rtb_gather_open(rtb_ctx *ctx, const void *handle64, void **ptr);
 int rtb_gather_close(rtb_ctx *ctx, void *ptr, int32_t own);
 int rtb_set_gather(rtb_ctx *ctx, int32_t world, double *const *bases, int64_t R_total, int64_t offset);
+/* The same for block-cyclic shards (raytracing_b200.dist.cyclic_indices): local ray r of rank `rank` is global ray
+   ((r / block) * nranks + rank) * block + r % block; block must be a power of two. */
+int rtb_set_gather_cyclic(rtb_ctx *ctx, int32_t world, double *const *bases, int64_t R_total, int64_t block,
+                          int32_t nranks, int32_t rank);
 
 /*
  * Measured FP64 pipe peak (dependent-free DFMA streams on every SM), the roofline denominator

@@ -368,10 +368,10 @@ int64_t rto_trace(const rto_params *p, const rto_spline *z, const rto_spline *gu
             row[0] = s.x; row[1] = s.y; row[2] = mx; row[3] = my; row[4] = T; row[5] = s.ang;
             if (s_ray) for (int c = 0; c < 6; ++c) s_ray[((size_t)i * 6 + c) * R + k] = row[c];
             if (px) { px[i] = s.x; py[i] = s.y; }
+            if (m == 7 && i < loop_iter) continue; /* the bootstrap rows are written before the loop that tests the box, RT:838-866 */
             if (s.x > p->limx_s || s.x < p->limx_i || s.y > p->limy_s || s.y < p->limy_i) break; /* RT:878 */
         }
         if (i >= M) i = M - 1; /* loop ran to completion: python leaves i = max_size-1 */
-        (void)loop_iter;
         d_ray[0 * R + k] = dist_real; d_ray[1 * R + k] = dist_sim; d_ray[2 * R + k] = (double)i; /* RT:888-890 */
         if (final) for (int c = 0; c < 6; ++c) final[c * R + k] = row[c];
         if (px) { errors[k] = snell_error(theta0[k], px, py, i); free(px); free(py); }

@@ -7,14 +7,18 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTB_LIB_PATH") or os.path.join(_HERE, "csrc", "librtb.so")  # override: kernel tuning only
 
 RTB_PTR_HOST, RTB_PTR_DEVICE = 0, 1
-RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO = 1, 2, 4
+RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO, RTB_F_STATIC_GRID = 1, 2, 4, 8
+RTB_OPT_QUEUE, RTB_OPT_TRAJ_STORE = 1, 2
+RTB_SWEEP_SNELL, RTB_SWEEP_CLOSURE, RTB_SWEEP_PX_CV = 1, 2, 3
+RTB_ABI_VERSION = 2
 RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -3, -4
 
 # every symbol include/rtb.h declares
 EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb_abi_version",
            "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront",
            "rtb_fit_field", "rtb_gradient", "rtb_get_field",
-           "rtb_gather_alloc", "rtb_gather_open", "rtb_gather_close", "rtb_set_gather")
+           "rtb_gather_alloc", "rtb_gather_open", "rtb_gather_close", "rtb_set_gather", "rtb_set_gather_cyclic",
+           "rtb_sweep", "rtb_set_option", "rtb_build_id")
 
 
 class RtbSpline(C.Structure):
@@ -31,7 +35,13 @@ class RtbParams(C.Structure):
 
 class RtbStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double), ("ray_steps", C.c_int64),
-                ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64)]
+                ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
+                ("nonfinite_rays", C.c_int64)]
+
+
+class RtbSweepSpec(C.Structure):
+    _fields_ = [("steps", C.c_void_p), ("max_sizes", C.c_void_p), ("C", C.c_int64), ("metric", C.c_int32),
+                ("skip_lo", C.c_int64), ("skip_hi", C.c_int64)]
 
 
 class RtbShootProblem(C.Structure):
@@ -98,5 +108,17 @@ def load():
     lib.rtb_gather_close.argtypes = [vp, vp, i32]
     lib.rtb_set_gather.restype = C.c_int
     lib.rtb_set_gather.argtypes = [vp, i32, C.POINTER(vp), i64, i64]
+    lib.rtb_set_gather_cyclic.restype = C.c_int
+    lib.rtb_set_gather_cyclic.argtypes = [vp, i32, C.POINTER(vp), i64, i64, i32, i32]
+    lib.rtb_sweep.restype = C.c_int
+    lib.rtb_sweep.argtypes = [vp, C.POINTER(RtbParams), vp, vp, vp, i64, C.POINTER(RtbSweepSpec), vp, vp, vp,
+                              C.POINTER(RtbStats)]
+    lib.rtb_set_option.restype = C.c_int
+    lib.rtb_set_option.argtypes = [vp, i32, i32]
+    lib.rtb_build_id.restype = C.c_char_p
+    lib.rtb_build_id.argtypes = []
+    if lib.rtb_abi_version() != RTB_ABI_VERSION:
+        raise ImportError("raytracing_b200: %s has ABI version %d, this package binds version %d -- rebuild it"
+                          % (LIB_PATH, lib.rtb_abi_version(), RTB_ABI_VERSION))
     _lib = lib
     return lib

@@ -81,6 +81,20 @@ def trazar(selected_func, z, grd, show, step, divisor, user_choice, fan=None, en
     return r.s_ray, r.d_ray, compute_times, r.errors
 
 
+def _simulated_angles(r):
+    """angsim of RT_bench.py:912-916 for every ray, from the stored trajectory (None without the stride-1 s_ray)."""
+    if r.s_ray is None or r.s_ray.shape[0] <= int(r.d_ray[2].max()):
+        return None
+    out = np.empty(r.d_ray.shape[1])
+    for k in range(out.size):
+        i = r.d_ray[2, k]
+        ia, ib = int(9 * i / 10), int(9.5 * i / 10)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            out[k] = 180 * np.arctan(np.abs((r.s_ray[ib, 0, k] - r.s_ray[ia, 0, k]) /
+                                            (r.s_ray[ib, 1, k] - r.s_ray[ia, 1, k]))) / np.pi
+    return out
+
+
 def _format_num(num):  # RT_bench.py:929-943
     if num < 0:
         return "{: >10.8f}".format(num) if abs(num) < 10 else "{: >10.7f}".format(num)
@@ -88,7 +102,9 @@ def _format_num(num):  # RT_bench.py:929-943
 
 
 def _print_snell_table(r, theta0):
-    """RT_bench.py:921-945."""
+    """RT_bench.py:921-945.  SimAng needs the two sample rows of the trajectory; without the stride-1 s_ray (FINAL or
+    strided output) the column shows the two values error and expected angle allow, SnellAng -+ Err."""
+    sim = _simulated_angles(r)
     for k in range(r.d_ray.shape[1]):
         a, b = r.last_row[0, k], r.last_row[1, k]
         e = r.errors[k]
@@ -99,8 +115,8 @@ def _print_snell_table(r, theta0):
             d = 0
         else:
             d = 180 * np.arcsin(np.sqrt(2) * np.sin(np.pi / 2 - th)) / np.pi
-        # the simulated angle is recovered from error = |angsim - angreal| only for display
-        print(f"Coords: [ {_format_num(a)} , {_format_num(b)} ] | SnellAng: {_format_num(d)} | "
+        c = _format_num(sim[k]) if sim is not None else "%s|%s" % (_format_num(d - e).strip(), _format_num(d + e).strip())
+        print(f"Coords: [ {_format_num(a)} , {_format_num(b)} ] | SimAng: {c} | SnellAng: {_format_num(d)} | "
               f"Err: {_format_num(e)} | InitAng: {_format_num(th * 180 / np.pi)}")
 
 
@@ -172,35 +188,49 @@ def find_index_vert(errors, max_deviation):
     return None
 
 
-def sweep_metrics(option, z, grd, user_choice, delta_s_options, divisors, fan=None, engine=None):
-    """The executor.map(search_delta, ...) of RT_bench.py:1317-1318 as ONE batched GPU trace over
-    candidates x rays (per-ray step/max_size), reduced to what the selection rules consume:
+def sweep_metrics(option, z, grd, user_choice, delta_s_options, divisors, fan=None, engine=None, group=None):
+    """The executor.map(search_delta, ...) of RT_bench.py:1317-1318 as batched GPU traces over candidates x rays with
+    the per-candidate reductions done on the device (rtb_sweep), reduced to what the selection rules consume:
       interface -> (error_prom[C], max_error[C]); fisheye -> closure %[C];
       vert/aniso -> scenario_average_CV[C] (RT_bench.py:1354-1360).
+    With `group` (a torch.distributed process group) the fan is sharded over the ranks in contiguous blocks and the
+    per-candidate partial sums / maxima / counts are all-reduced (dist.reduce_sum_max).
     """
     eng = engine or get_engine()
     uc, gamma, box = _scenario(user_choice)
     eng.set_field(z, grd)
     theta0, x0, y0 = fan if fan is not None else default_fan(uc)
-    R, Cn = len(theta0), len(delta_s_options)
-    steps = np.repeat(np.asarray(delta_s_options, dtype=np.float64), R)
-    msz = np.repeat(np.array([max_size_for(uc, s, d + 1) for s, d in zip(delta_s_options, divisors)],
-                             dtype=np.int64), R)
-    r = eng.trace(option, np.tile(theta0, Cn), np.tile(x0, Cn), np.tile(y0, Cn), None, int(msz.max()), gamma, box,
-                  interface=(uc == "1"), full=False, want_px_stats=(uc in "34"), want_errors=(uc == "1"),
-                  steps=steps, max_sizes=msz)
-    if uc == "1":
-        e = r.errors.reshape(Cn, R)
-        return [np.mean(row) for row in e], [np.max(row) for row in e]
-    if uc == "2":
-        last = r.last_row.reshape(6, Cn, R)
-        done = r.d_ray[2].reshape(Cn, R)[:, 0] == (msz.reshape(Cn, R)[:, 0] - 1)  # rays[-1] is row max_size-1
-        xy = np.where(done[None, :], last[0:2, :, 0], 0.0)
-        return [100 * np.linalg.norm(np.array([1, 0]) - xy[:, j]) / (2 * np.pi) for j in range(Cn)]
-    st = r.px_stats.reshape(3, Cn, R)
+    theta0 = np.asarray(theta0, dtype=np.float64)
+    R = len(theta0)
+    x0, y0 = (np.broadcast_to(np.asarray(a, dtype=np.float64), (R,)) for a in (x0, y0))
+    msz = np.array([max_size_for(uc, s, d + 1) for s, d in zip(delta_s_options, divisors)], dtype=np.int64)
+    metric = {"1": "snell", "2": "closure"}.get(uc, "px_cv")
+    lo, hi = 0, R
+    if group is not None:
+        import torch.distributed as dist
+        from .dist import shard_bounds
+        lo, hi = shard_bounds(R, dist.get_world_size(group), dist.get_rank(group))
+    # the reference leaves its first and last ray out of the CV average (range(1, ray_count - 1), RT:1356);
+    # the closure error is that of the fan's first ray (rays[-1, 0:2, 0], RT:956)
+    skip_lo = 1 if (metric == "px_cv" and lo == 0) else 0
+    skip_hi = 1 if (metric == "px_cv" and hi == R) else 0
+    if metric == "closure":
+        hi = min(hi, 1) if lo == 0 else lo
+    sm, mx, cnt, _stats = eng.sweep(option, theta0[lo:hi], x0[lo:hi], y0[lo:hi], delta_s_options, msz, gamma, box, metric,
+                                    skip_lo=skip_lo, skip_hi=skip_hi)
+    if group is not None:
+        import torch
+        from .dist import reduce_sum_max
+        dev = torch.device("cuda", eng.device) if torch.distributed.get_backend(group) == "nccl" else torch.device("cpu")
+        st = torch.as_tensor(np.stack([sm, cnt.astype(np.float64)]), device=dev)
+        mt = torch.as_tensor(mx, device=dev)
+        reduce_sum_max(st, mt, group)
+        sm, cnt, mx = st[0].cpu().numpy(), st[1].cpu().numpy(), mt.cpu().numpy()
     with np.errstate(invalid="ignore", divide="ignore"):
-        cv = 100 * st[2] / st[1]
-    return [np.mean(cv[j, 1:R - 1]) for j in range(Cn)]
+        mean = sm / cnt
+    if uc == "1":
+        return list(mean), list(mx)
+    return list(mean)
 
 
 def find_delta_s(option, z, grd, user_choice, fan=None, engine=None):
@@ -236,13 +266,16 @@ def remove_outliers_iqr(data):
     return data[(data >= q1 - 1.5 * iqr) & (data <= q3 + 1.5 * iqr)]
 
 
-def benchmark_statistic(sample_fn, trial=100, replicas=1, max_rounds=50):
+def benchmark_statistic(sample_fn, trial=100, replicas=1, max_rounds=None):
     """RT_bench.py:1516-1538 with `sample_fn()` -> seconds replacing one worker's np.sum(result[2]):
     rounds of trial*replicas samples, IQR filter, median of the last 30 %, repeat until two
-    consecutive medians agree to 0.5 %, return their mean."""
+    consecutive medians agree to 0.5 %, return their mean.  Like the reference the loop is unbounded by default
+    (`while True`, RT:1517); `max_rounds` is an optional safety cap for callers with noisy samplers (a deviation:
+    the reference has none)."""
+    import itertools
     benchmarks = []
     arr = np.zeros(trial * replicas)
-    for _ in range(max_rounds):
+    for _ in (itertools.count() if max_rounds is None else range(max_rounds)):
         for idx in range(arr.size):
             arr[idx] = sample_fn()
         cleaned = remove_outliers_iqr(arr)

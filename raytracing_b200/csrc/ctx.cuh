@@ -13,7 +13,7 @@
 #include <vector>
 
 namespace rtb {
-#define RTB_DECL(K) cudaError_t launch_trace_m##K(const TraceArgs &, bool, bool, bool, int, cudaStream_t);
+#define RTB_DECL(K) cudaError_t launch_trace_m##K(const TraceArgs &, const LaunchCfg &, cudaStream_t);
 RTB_DECL(1) RTB_DECL(2) RTB_DECL(3) RTB_DECL(4) RTB_DECL(5) RTB_DECL(6)
 RTB_DECL(7) RTB_DECL(8) RTB_DECL(9) RTB_DECL(10) RTB_DECL(11)
 #undef RTB_DECL
@@ -24,6 +24,8 @@ static const launch_fn kLaunch[12] = {nullptr, launch_trace_m1, launch_trace_m2,
 
 using namespace rtb;
 
+#define RTB_COUNTER_SLOTS 256
+
 struct rtb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -33,14 +35,19 @@ struct rtb_ctx {
     DevField f;
     DevField *f_dev = nullptr;
     std::vector<void *> field_allocs;
-    unsigned long long *d_total = nullptr;
+    unsigned long long *d_total = nullptr; // [0] ray-steps of the call, [1] rays that ended non-finite, [2..] queue heads
     int block = RTB_BLOCK;
+    int sm_count = 148;
+    int queue_slot = 2; // d_total slot of the last ray-queue launch (round robin over RTB_COUNTER_SLOTS - 2)
+    int queue_mode = 0; // rtb_set_option(RTB_OPT_QUEUE): 0 = auto, 1 = always the ray-queue kernel, 2 = never
+    int traj_mode = 0;  // rtb_set_option(RTB_OPT_TRAJ_STORE): 0 = auto (bulk copies when aligned), 1 = per-lane stores
     // host-buffer calls on large fans are cut into chunks whose H2D copy, kernel and D2H copy overlap (rtb_trace)
     cudaStream_t pipe[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // fork + one join per pipe stream
     // fused result gather (rtb_set_gather): peer base pointers, total rays, this rank's ray offset
     double *gather[RTB_MAX_PEERS] = {};
     int gather_world = 0;
+    int gather_bshift = -1, gather_nranks = 1, gather_rank = 0;
     int64_t gather_R = 0, gather_off = 0;
     std::string err;
     // grow-only pool of staging buffers (RTB_PTR_HOST calls): cudaMalloc/cudaFree per call cost ms
@@ -70,6 +77,14 @@ static inline int pick_lane_shift(int64_t R)
     while (shift < 5 && (R << (shift + 1)) <= (int64_t)148 * 16 * 32) ++shift;
     return shift;
 }
+
+struct Staging;
+// Pieces of rtb_trace (rtb.cu) shared with shoot.cu and sweep.cu: common TraceArgs, one kernel launch (static grid or
+// ray queue), and integration + Snell metric on a prepared device fan.
+TraceArgs rtb_base_args(rtb_ctx *ctx, const rtb_params *p, int stride);
+int rtb_launch(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, TraceArgs a, bool traj);
+int rtb_trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const TraceArgs &a, double *d_err,
+                   bool has_errors, bool want_err, bool traj, int stride, Staging &sg, int64_t &launches);
 
 // Field construction pieces defined in rtb.cu and shared with fit.cu.
 void rtb_free_field(rtb_ctx *ctx);
@@ -112,6 +127,15 @@ struct Staging {
     {
         for (void *p : tmp)
             for (auto &b : ctx->pool) if (b.p == p) b.used = false;
+    }
+    // Scratch of one round of a loop: buffers allocated after mark() go back to the pool at release() and may be
+    // handed out again by the next round -- safe because every round runs on this Staging's one stream.
+    size_t mark() const { return tmp.size(); }
+    void release(size_t m)
+    {
+        for (size_t k = m; k < tmp.size(); ++k)
+            for (auto &b : ctx->pool) if (b.p == tmp[k]) b.used = false;
+        tmp.resize(m);
     }
     void *alloc(size_t bytes)
     {

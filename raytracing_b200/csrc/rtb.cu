@@ -4,7 +4,18 @@
 #include "ctx.cuh"
 #include "cell_tables.cuh"
 
+typedef CUresult (*cuTensorMapEncodeTiled_t)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                             const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                             CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                             CUtensorMapFloatOOBfill);
+
 extern "C" int rtb_abi_version(void) { return RTB_ABI_VERSION; }
+
+// Hash of the CUDA sources this library was compiled from (csrc/Makefile writes build_id.h before compiling):
+// __graft_entry__.build()/smoke() and tests/test_cabi.py compare it with the hash of the sources in the tree, so a
+// stale librtb.so cannot pass for the current code.
+#include "build_id.h"
+extern "C" const char *rtb_build_id(void) { return RTB_BUILD_ID; }
 
 extern "C" const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
@@ -24,10 +35,11 @@ extern "C" int rtb_create(int device, rtb_ctx **out)
     }
     ctx->own_stream = true;
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
-    if (cudaMalloc(&ctx->d_total, sizeof(unsigned long long)) != cudaSuccess) {
+    if (cudaMalloc(&ctx->d_total, sizeof(unsigned long long) * RTB_COUNTER_SLOTS) != cudaSuccess) {
         delete ctx;
         return RTB_ERR_CUDA;
     }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     *out = ctx;
     return RTB_OK;
 }
@@ -51,6 +63,14 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
     for (auto &ps : ctx->pipe) if (ps) cudaStreamDestroy(ps);
     for (auto &pe : ctx->pipe_ev) if (pe) cudaEventDestroy(pe);
     delete ctx;
+}
+
+extern "C" int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value)
+{
+    if (!ctx) return RTB_ERR_ARG;
+    if (option == RTB_OPT_QUEUE && value >= 0 && value <= 2) { ctx->queue_mode = value; return RTB_OK; }
+    if (option == RTB_OPT_TRAJ_STORE && value >= 0 && value <= 1) { ctx->traj_mode = value; return RTB_OK; }
+    return fail(ctx, RTB_ERR_ARG, "rtb_set_option: unknown option or value");
 }
 
 extern "C" int rtb_set_stream(rtb_ctx *ctx, void *cuda_stream)
@@ -249,8 +269,8 @@ __global__ void snell_rows_kernel(const double *d_ray, int64_t R, int *cap_rows)
     cap_rows[r] = ia;
     cap_rows[R + r] = ib;
 }
-__global__ void snell_from_traj_kernel(const double *s_ray, const double *d_ray, const double *theta0, int64_t R,
-                                       double *errors)
+__global__ void snell_from_traj_kernel(const double *s_ray, const double *d_ray, const double *theta0, int64_t cand_R,
+                                       int64_t R, double *errors)
 {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= R) return;
@@ -259,33 +279,84 @@ __global__ void snell_from_traj_kernel(const double *s_ray, const double *d_ray,
     const double distx = s_ray[((size_t)ib * 6 + 0) * R + r] - s_ray[((size_t)ia * 6 + 0) * R + r];
     const double disty = s_ray[((size_t)ib * 6 + 1) * R + r] - s_ray[((size_t)ia * 6 + 1) * R + r];
     const double angsim = 180 * atan(fabs(distx / disty)) / RTB_PI;
-    errors[r] = fabs(angsim - snell_expected(theta0[r]));
+    errors[r] = fabs(angsim - snell_expected(theta0[cand_R > 0 ? r % cand_R : r]));
 }
-__global__ void snell_from_cap_kernel(const double *cap, const double *theta0, int64_t R, double *errors)
+__global__ void snell_from_cap_kernel(const double *cap, const double *theta0, int64_t cand_R, int64_t R, double *errors)
 {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= R) return;
     const double distx = cap[2 * R + r] - cap[r];
     const double disty = cap[3 * R + r] - cap[R + r];
     const double angsim = 180 * atan(fabs(distx / disty)) / RTB_PI;
-    errors[r] = fabs(angsim - snell_expected(theta0[r]));
+    errors[r] = fabs(angsim - snell_expected(theta0[cand_R > 0 ? r % cand_R : r]));
 }
 
 // ---------------------------------------------------------------------------------------
 // rtb_trace: trazar RT_bench.py:766-948
 // ---------------------------------------------------------------------------------------
+// Launch configuration of one integration kernel launch: which kernel (static grid / ray queue), block size, and --
+// for the queue kernel -- a freshly zeroed queue head.
+int rtb_launch(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, TraceArgs a, bool traj)
+{
+    LaunchCfg c;
+    c.iso = p->gamma == 1.0;
+    c.traj = traj;
+    c.exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
+    c.block = a.lane_shift ? 32 : ctx->block;
+    // Ray queue + warp compaction: FINAL-type outputs of the default kernels on fans of at least a wave; the static
+    // grid keeps trajectories (coalesced rows need thread <-> ray fixed), the faithful kernels and spread small fans.
+    const bool can_queue = !traj && !c.exact && a.lane_shift == 0 && a.stage;
+    c.queue = can_queue && (ctx->queue_mode == 1 || (ctx->queue_mode == 0 && (p->flags & RTB_F_STATIC_GRID) == 0));
+    c.queue_blocks = ctx->sm_count * RTB_QUEUE_MIN_BLOCKS;
+    if (c.queue) {
+        const int64_t need = (a.R + RTB_BLOCK - 1) / RTB_BLOCK;
+        if (need < c.queue_blocks) c.queue_blocks = (int)need;
+        ctx->queue_slot = 2 + (ctx->queue_slot - 2 + 1) % (RTB_COUNTER_SLOTS - 2);
+        a.queue_head = ctx->d_total + ctx->queue_slot;
+        CK(cudaMemsetAsync(a.queue_head, 0, sizeof(unsigned long long), st));
+    }
+    // Trajectory rows through shared memory + 2-D TMA stores (traj_stage.cuh): s_ray as the matrix (rows*6, R) of
+    // doubles, tiles of (6*RTB_TRAJ_ROWS) x 32 and single rows of 6 x 32.  Needs 16-byte aligned rows.
+    a.traj_bulk = 0;
+    const int64_t rows = traj ? ((int64_t)a.max_size + a.out_stride - 1) / a.out_stride : 0;
+    if (traj && ctx->traj_mode == 0 && a.lane_shift == 0 && (a.R % 2) == 0 && ((uintptr_t)a.s_ray % 16) == 0 &&
+        a.R < ((int64_t)1 << 31) && rows * 6 < ((int64_t)1 << 31)) {
+        static cuTensorMapEncodeTiled_t encode = nullptr;
+        if (!encode) {
+            void *fn = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+                qr == cudaDriverEntryPointSuccess)
+                encode = (cuTensorMapEncodeTiled_t)fn;
+            (void)cudaGetLastError();
+        }
+        if (encode) {
+            const cuuint64_t dims[2] = {(cuuint64_t)a.R, (cuuint64_t)(rows * 6)};
+            const cuuint64_t strides[1] = {(cuuint64_t)a.R * sizeof(double)};
+            const cuuint32_t box[2] = {32, 6 * RTB_TRAJ_ROWS}, one[2] = {32, 6}, es[2] = {1, 1};
+            const CUresult r1 = encode(&a.tmaps.box, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, a.s_ray, dims, strides, box, es,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            const CUresult r2 = encode(&a.tmaps.row, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, a.s_ray, dims, strides, one, es,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            a.traj_bulk = (r1 == CUDA_SUCCESS && r2 == CUDA_SUCCESS) ? 1 : 0;
+        }
+    }
+    CK(kLaunch[p->method](a, c, st));
+    return RTB_OK;
+}
+
 // The kernels of one trace on stream `st`, every pointer of `a` on the device: the integration and, when asked, the
 // Snell error metric (RT_bench.py:896-919).
-static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const TraceArgs &a, double *d_err,
-                      bool has_errors, bool want_err, bool traj, int stride, Staging &sg, int64_t &launches)
+int rtb_trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const TraceArgs &a, double *d_err,
+                   bool has_errors, bool want_err, bool traj, int stride, Staging &sg, int64_t &launches)
 {
     const int64_t R = a.R;
-    const bool iso = p->gamma == 1.0;
-    const bool exact = (p->flags & RTB_F_EXACT_BASIS) != 0;
-    const int block = a.lane_shift ? 32 : ctx->block;
     const bool two_pass = has_errors && want_err && !(traj && stride == 1);
+    int rc;
     TraceArgs a1 = a;
-    if (two_pass) {
+    if (two_pass && !traj) { // a trajectory pass writes no checkpoints: pass 2 then integrates from the origin
         // pass 1 leaves the ray state every 2^shift steps so that pass 2 starts near its first sample row instead
         // of at the ray's origin: at most 32 checkpoints of 136 B per ray, 1 GB in all, else coarser or none
         int shift = 8;
@@ -298,14 +369,14 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
             else { (void)cudaGetLastError(); sg.err = cudaSuccess; } // no room: pass 2 integrates from the origin
         }
     }
-    CK(kLaunch[p->method](a1, iso, traj, exact, block, st));
+    if ((rc = rtb_launch(ctx, st, p, a1, traj))) return rc;
     ++launches;
     const unsigned g1 = (unsigned)((R + 127) / 128);
     if (has_errors) {
         if (!want_err) {
             CK(cudaMemsetAsync(d_err, 0, sizeof(double) * R, st));
         } else if (traj && stride == 1) {
-            snell_from_traj_kernel<<<g1, 128, 0, st>>>(a.s_ray, a.d_ray, a.theta0, R, d_err);
+            snell_from_traj_kernel<<<g1, 128, 0, st>>>(a.s_ray, a.d_ray, a.theta0, a.cand_R, R, d_err);
             ++launches;
         } else {
             // two-pass: the sample rows int(9i/10), int(9.5i/10) depend on the final step count i,
@@ -315,15 +386,33 @@ static int trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const 
             if (!cap_rows || !cap_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_trace: capture buffers", sg.err);
             snell_rows_kernel<<<g1, 128, 0, st>>>(a.d_ray, R, cap_rows);
             TraceArgs b = a1;
-            b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr;
-            b.total_steps = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
-            CK(kLaunch[p->method](b, iso, false, exact, block, st));
-            snell_from_cap_kernel<<<g1, 128, 0, st>>>(cap_out, a.theta0, R, d_err);
+            b.s_ray = nullptr; b.d_ray = nullptr; b.last_row = nullptr; b.px_stats = nullptr; b.exit_out = nullptr;
+            b.total_steps = nullptr; b.nonfinite = nullptr; b.cap_rows = cap_rows; b.cap_out = cap_out;
+            if ((rc = rtb_launch(ctx, st, p, b, false))) return rc;
+            snell_from_cap_kernel<<<g1, 128, 0, st>>>(cap_out, a.theta0, a.cand_R, R, d_err);
             launches += 3;
         }
         CK(cudaGetLastError());
     }
     return RTB_OK;
+}
+
+// Common part of the TraceArgs of a call.
+TraceArgs rtb_base_args(rtb_ctx *ctx, const rtb_params *p, int stride)
+{
+    TraceArgs base;
+    std::memset(&base, 0, sizeof(base));
+    base.f = ctx->f;
+    base.f_dev = ctx->f_dev;
+    base.max_size = (int)p->max_size; base.out_stride = stride;
+    base.tail_zero = (p->flags & RTB_F_NO_TAIL_ZERO) ? 0 : 1;
+    base.step = p->step; base.gamma = p->gamma;
+    base.limx_i = p->limx_i; base.limx_s = p->limx_s; base.limy_i = p->limy_i; base.limy_s = p->limy_s;
+    base.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
+    base.total_steps = ctx->d_total;
+    base.nonfinite = ctx->d_total + 1;
+    base.gather_bshift = -1;
+    return base;
 }
 
 extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0,
@@ -349,24 +438,18 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     const int64_t rows = traj ? (p->max_size + stride - 1) / stride : 0;
 
     CK(cudaEventRecord(ctx->ev[0], st));
-    CK(cudaMemsetAsync(ctx->d_total, 0, sizeof(unsigned long long), st));
-    TraceArgs base;
-    std::memset(&base, 0, sizeof(base));
-    base.f = ctx->f;
-    base.f_dev = ctx->f_dev;
-    base.max_size = (int)p->max_size; base.out_stride = stride;
-    base.tail_zero = (p->flags & RTB_F_NO_TAIL_ZERO) ? 0 : 1;
-    base.step = p->step; base.gamma = p->gamma;
-    base.limx_i = p->limx_i; base.limx_s = p->limx_s; base.limy_i = p->limy_i; base.limy_s = p->limy_s;
-    base.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
-    base.total_steps = ctx->d_total;
+    CK(cudaMemsetAsync(ctx->d_total, 0, 2 * sizeof(unsigned long long), st));
+    TraceArgs base = rtb_base_args(ctx, p, stride);
     if (ctx->gather_world > 0 && !host && d_ray) {
-        if (ctx->gather_off + R > ctx->gather_R) return fail(ctx, RTB_ERR_ARG, "rtb_trace: fan exceeds the gather window (rtb_set_gather)");
+        if (ctx->gather_bshift < 0 && ctx->gather_off + R > ctx->gather_R)
+            return fail(ctx, RTB_ERR_ARG, "rtb_trace: fan exceeds the gather window (rtb_set_gather)");
         for (int pe = 0; pe < ctx->gather_world; ++pe) base.gather[pe] = ctx->gather[pe];
         base.gather_world = ctx->gather_world; base.gather_R = ctx->gather_R; base.gather_off = ctx->gather_off;
+        base.gather_bshift = ctx->gather_bshift; base.gather_nranks = ctx->gather_nranks; base.gather_rank = ctx->gather_rank;
     }
     base.stage = R >= (1 << 16); // below ~one wave of warps a launch is a latency chain: no staging detour
     int64_t launches = 0, h2d = 0, d2h = 0;
+    unsigned long long counters[2] = {0, 0};
     int rc;
 
     // Host buffers, no trajectory, a large fan: cut the rays into chunks and run each chunk's H2D copy, kernels and
@@ -405,7 +488,7 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
             if (sg.err != cudaSuccess)
                 return bail(fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
                                  "rtb_trace: staging", sg.err));
-            if ((rc = trace_core(ctx, ps, p, a, d_err, errors != nullptr, want_err, false, stride, sg, launches)))
+            if ((rc = rtb_trace_core(ctx, ps, p, a, d_err, errors != nullptr, want_err, false, stride, sg, launches)))
                 return bail(rc);
             sg.copy_back();
         }
@@ -414,9 +497,8 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
             je = cudaEventRecord(ctx->pipe_ev[1 + j], ctx->pipe[j]);
             if (je == cudaSuccess) je = cudaStreamWaitEvent(st, ctx->pipe_ev[1 + j], 0);
         }
-        unsigned long long total = 0;
         if (je == cudaSuccess) je = cudaEventRecord(ctx->ev[2], st);
-        if (je == cudaSuccess) je = cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st);
+        if (je == cudaSuccess) je = cudaMemcpyAsync(counters, ctx->d_total, sizeof(counters), cudaMemcpyDeviceToHost, st);
         if (je == cudaSuccess) je = cudaEventRecord(ctx->ev[3], st);
         if (je == cudaSuccess) je = cudaStreamSynchronize(st);
         if (je != cudaSuccess) return bail(fail(ctx, RTB_ERR_CUDA, "rtb_trace: joining the chunk streams", je));
@@ -424,9 +506,10 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
             if (sg->err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg->err);
             h2d += sg->h2d; d2h += sg->d2h;
         }
-        if (stats) stats->ray_steps = (int64_t)total;
     } else {
         Staging sg(ctx, host);
+        // an error after the first launch must not hand buffers with work in flight back to the pool
+        auto bail = [&](int code) { cudaStreamSynchronize(st); return code; };
         TraceArgs a = base;
         a.theta0 = sg.in(theta0, R); a.x0 = sg.in(x0, R); a.y0 = sg.in(y0, R);
         a.steps = sg.in(p->steps, R); a.max_sizes = sg.in(p->max_sizes, R);
@@ -437,24 +520,24 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
         a.last_row = sg.out(last_row, (size_t)6 * R);
         a.px_stats = sg.out(px_stats, (size_t)3 * R);
         double *d_err = sg.out(errors, (size_t)R);
-        if (sg.err != cudaSuccess) return fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
-                                                "rtb_trace: staging", sg.err);
+        if (sg.err != cudaSuccess) return bail(fail(ctx, sg.err == cudaErrorMemoryAllocation ? RTB_ERR_NOMEM : RTB_ERR_CUDA,
+                                                     "rtb_trace: staging", sg.err));
         CK(cudaEventRecord(ctx->ev[1], st));
-        if ((rc = trace_core(ctx, st, p, a, d_err, errors != nullptr, want_err, traj, stride, sg, launches))) return rc;
+        if ((rc = rtb_trace_core(ctx, st, p, a, d_err, errors != nullptr, want_err, traj, stride, sg, launches))) return bail(rc);
         CK(cudaEventRecord(ctx->ev[2], st));
         sg.copy_back();
-        unsigned long long total = 0;
-        CK(cudaMemcpyAsync(&total, ctx->d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(counters, ctx->d_total, sizeof(counters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(ctx->ev[3], st));
         CK(cudaStreamSynchronize(st));
         if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "rtb_trace: copy", sg.err);
         h2d = sg.h2d; d2h = sg.d2h;
-        if (stats) stats->ray_steps = (int64_t)total;
     }
     if (stats) {
         float ms = 0;
         cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); stats->kernel_ms = ms;
         cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); stats->total_ms = ms;
+        stats->ray_steps = (int64_t)counters[0];
+        stats->nonfinite_rays = (int64_t)counters[1];
         stats->launches = launches;
         stats->h2d_bytes = h2d; stats->d2h_bytes = d2h;
     }
@@ -510,6 +593,25 @@ extern "C" int rtb_set_gather(rtb_ctx *ctx, int32_t world, double *const *bases,
         if (!bases[pe]) return fail(ctx, RTB_ERR_ARG, "rtb_set_gather: null peer buffer");
     for (int pe = 0; pe < RTB_MAX_PEERS; ++pe) ctx->gather[pe] = pe < world ? bases[pe] : nullptr;
     ctx->gather_world = world; ctx->gather_R = R_total; ctx->gather_off = offset;
+    ctx->gather_bshift = -1; ctx->gather_nranks = 1; ctx->gather_rank = 0;
+    return RTB_OK;
+}
+
+extern "C" int rtb_set_gather_cyclic(rtb_ctx *ctx, int32_t world, double *const *bases, int64_t R_total, int64_t block,
+                                     int32_t nranks, int32_t rank)
+{
+    if (!ctx) return RTB_ERR_ARG;
+    if (world < 1 || world > RTB_MAX_PEERS || !bases || R_total <= 0)
+        return fail(ctx, RTB_ERR_ARG, "rtb_set_gather_cyclic: bad window");
+    if (block < 1 || (block & (block - 1)) != 0 || nranks < 1 || rank < 0 || rank >= nranks)
+        return fail(ctx, RTB_ERR_ARG, "rtb_set_gather_cyclic: block must be a power of two, 0 <= rank < nranks");
+    for (int pe = 0; pe < world; ++pe)
+        if (!bases[pe]) return fail(ctx, RTB_ERR_ARG, "rtb_set_gather_cyclic: null peer buffer");
+    for (int pe = 0; pe < RTB_MAX_PEERS; ++pe) ctx->gather[pe] = pe < world ? bases[pe] : nullptr;
+    ctx->gather_world = world; ctx->gather_R = R_total; ctx->gather_off = 0;
+    int b = 0;
+    while (((int64_t)1 << b) < block) ++b;
+    ctx->gather_bshift = b; ctx->gather_nranks = nranks; ctx->gather_rank = rank;
     return RTB_OK;
 }
 

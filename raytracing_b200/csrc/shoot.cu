@@ -23,27 +23,24 @@ struct FanBuffers { // device pointers of one batched launch
 };
 
 // Launch the integrator on prepared device buffers (FINAL mode + exit points), no staging, no sync.
-int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n, int64_t max_size)
+int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n, int64_t max_size, cudaStream_t st = nullptr)
 {
-    TraceArgs a;
-    std::memset(&a, 0, sizeof(a));
-    a.f = ctx->f;
-    a.f_dev = ctx->f_dev;
+    rtb_params pp = *p;
+    pp.max_size = max_size;
+    TraceArgs a = rtb_base_args(ctx, &pp, 1);
+    a.tail_zero = 0;
     a.theta0 = b.theta; a.x0 = b.x0; a.y0 = b.y0;
     a.steps = b.steps; a.max_sizes = b.max_sizes;
-    a.R = n; a.max_size = (int)max_size; a.out_stride = 1; a.tail_zero = 0;
-    a.step = p->step; a.gamma = p->gamma;
-    a.limx_i = p->limx_i; a.limx_s = p->limx_s; a.limy_i = p->limy_i; a.limy_s = p->limy_s;
-    a.in = make_cell_box(ctx->f, p->limx_i, p->limx_s, p->limy_i, p->limy_s);
+    a.R = n;
     a.d_ray = b.d_ray;
     a.exit_out = b.exit_out;
-    a.total_steps = ctx->d_total;
-    // small batches: rays spread over the warps of all SMs (pick_lane_shift), 32-thread blocks
+    a.nonfinite = nullptr;
+    // small batches: rays spread over the warps of all SMs (pick_lane_shift), 32-thread blocks; large ones run on
+    // the ray queue (candidates of different length share warps at the candidate boundaries and, in the refinement,
+    // converged pairs take no steps at all: the warps compact)
     a.lane_shift = pick_lane_shift(n);
-    const int block = n < (int64_t)148 * 4 * 128 ? 32 : ctx->block;
-    cudaError_t e = kLaunch[p->method](a, p->gamma == 1.0, false, (p->flags & RTB_F_EXACT_BASIS) != 0, block, ctx->stream);
-    if (e != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, "shoot: trace launch", e);
-    return RTB_OK;
+    a.stage = n >= (1 << 16);
+    return rtb_launch(ctx, st ? st : ctx->stream, &pp, a, false);
 }
 
 // coarse fan: ray (c, j) = angle j with candidate c's step / max_size
@@ -97,13 +94,16 @@ __device__ __forceinline__ void golden_probes(double a, double b, double &c, dou
     d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
 }
 
+// Pairs [i0, i0 + n) of the (C, Tn) problem; `f` holds this group's 2n probe rays.  active[0] counts the pairs that
+// still iterate, active[1] takes the widest |c - d| of the group (positive doubles order like their bit patterns).
 __global__ void refine_init_kernel(const double *lo, const double *hi, const double *steps, const int64_t *max_sizes,
-                                   int64_t Tn, int64_t n, double sx, double sy, double *a, double *b, FanBuffers f,
+                                   int64_t Tn, int64_t i0, int64_t n, double sx, double sy, double *a, double *b, FanBuffers f,
                                    unsigned long long *active)
 {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int64_t c = i / Tn;
+    const int64_t c = (i0 + i) / Tn;
+    lo += i0; hi += i0; a += i0; b += i0;
     a[i] = lo[i]; b[i] = hi[i];
     double pc, pd;
     golden_probes(lo[i], hi[i], pc, pd);
@@ -113,17 +113,21 @@ __global__ void refine_init_kernel(const double *lo, const double *hi, const dou
     f.steps[i] = steps[c]; f.steps[n + i] = steps[c];
     const int64_t m = act ? max_sizes[c] : 1; // converged pairs stop tracing (max_size 1 = no step)
     f.max_sizes[i] = m; f.max_sizes[n + i] = m;
-    if (act) atomicAdd(active, 1ull);
+    if (act) {
+        atomicAdd(active, 1ull);
+        atomicMax(active + 1, (unsigned long long)__double_as_longlong(fabs(pc - pd)));
+    }
 }
 
-__global__ void refine_update_kernel(const double *tx, const double *ty, int64_t Tn, int64_t n, double *a, double *b,
-                                     FanBuffers f, unsigned long long *active)
+__global__ void refine_update_kernel(const double *tx, const double *ty, int64_t Tn, int64_t i0, int64_t n, double *a,
+                                     double *b, FanBuffers f, unsigned long long *active)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double pc = f.theta[i], pd = f.theta[n + i];
     if (!(fabs(pc - pd) > RTB_GOLD_TOL)) return; // while abs(c - d) > tol
-    const int64_t t = i % Tn;
+    const int64_t t = (i0 + i) % Tn;
+    a += i0; b += i0;
     const double px = tx[t], py = ty[t];
     const double *ex = f.exit_out, *ey = f.exit_out + 2 * n; // this launch had 2n rays: exit_out is (3, 2n)
     double dx = ex[i] - px, dy = ey[i] - py;
@@ -140,14 +144,16 @@ __global__ void refine_update_kernel(const double *tx, const double *ty, int64_t
     else { f.max_sizes[i] = 1; f.max_sizes[n + i] = 1; }
 }
 
-__global__ void refine_final_fill_kernel(const double *a, const double *b, const int64_t *max_sizes, int64_t Tn,
-                                         int64_t n, double *theta_out, FanBuffers f)
+__global__ void refine_final_fill_kernel(const double *a, const double *b, const double *steps, const int64_t *max_sizes,
+                                         int64_t Tn, int64_t n, double sx, double sy, double *theta_out, FanBuffers f)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double th = (b[i] + a[i]) / 2.0; // return (b + a) / 2  RT:199
     theta_out[i] = th;
     f.theta[i] = th;
+    f.x0[i] = sx; f.y0[i] = sy;
+    f.steps[i] = steps[i / Tn];
     f.max_sizes[i] = max_sizes[i / Tn];
 }
 
@@ -287,33 +293,94 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
     const double *d_tx = sg.in(q->target_x, Tn), *d_ty = sg.in(q->target_y, Tn);
     double *d_theta = sg.out(theta, n), *d_res = sg.out(result, 5 * n);
     double *d_a = (double *)sg.alloc(sizeof(double) * n), *d_b = (double *)sg.alloc(sizeof(double) * n);
-    unsigned long long *d_active = (unsigned long long *)sg.alloc(sizeof(unsigned long long));
-    FanBuffers fb = alloc_fan(sg, 2 * n);
-    if (sg.err != cudaSuccess || !fb.exit_out || !d_a || !d_b || !d_active)
-        return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_refine: staging", sg.err);
-    CK(cudaMemsetAsync(ctx->d_total, 0, sizeof(unsigned long long), st));
-    CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long), st));
-    CK(cudaEventRecord(ctx->ev[1], st));
-    const unsigned g = (unsigned)((n + 255) / 256);
-    int64_t launches = 1, iters = 0;
-    refine_init_kernel<<<g, 256, 0, st>>>(d_lo, d_hi, d_steps, d_msz, Tn, n, q->src_x, q->src_y, d_a, d_b, fb, d_active);
-    unsigned long long active = 0;
-    CK(cudaMemcpyAsync(&active, d_active, sizeof(active), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    // golden's while loop (RT:188): every pass re-traces both probes of every still-active pair
-    while (active > 0 && iters < 4096) {
-        CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long), st));
-        if ((rc = launch_fan(ctx, p, fb, 2 * n, M))) return rc;
-        refine_update_kernel<<<g, 256, 0, st>>>(d_tx, d_ty, Tn, n, d_a, d_b, fb, d_active);
-        CK(cudaMemcpyAsync(&active, d_active, sizeof(active), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        launches += 2;
-        ++iters;
+
+    // The pairs are independent, and every golden iteration of a pair is one re-trace of its two probe rays -- a
+    // launch that lasts as long as its longest ray however few rays it holds.  So the pairs are cut into up to four
+    // groups (contiguous in the candidate-major order: candidates of similar length) that iterate on their own
+    // streams: while one group's launch drains its long rays the others fill the SMs.  Nothing comes back to the host
+    // between iterations: golden's trip count follows from the bracket width alone (the loop test RT:188 is on
+    // |c - d|, which shrinks by GOLD_RATIO per pass whatever f does), so each group's count is fixed after its first
+    // pass over the brackets and one counter read at the very end confirms that no pair is left iterating.
+    const int G = (int)std::min<int64_t>(4, std::max<int64_t>(1, n / 4096));
+    for (auto &ps : ctx->pipe) if (!ps) CK(cudaStreamCreateWithFlags(&ps, cudaStreamNonBlocking));
+    for (auto &pe : ctx->pipe_ev) if (!pe) CK(cudaEventCreateWithFlags(&pe, cudaEventDisableTiming));
+    unsigned long long *d_active = (unsigned long long *)sg.alloc(sizeof(unsigned long long) * 2 * G);
+    struct Group { int64_t i0, n; FanBuffers fb; cudaStream_t st; int iters; };
+    std::vector<Group> gr(G);
+    bool ok = sg.err == cudaSuccess && d_a && d_b && d_active;
+    for (int g = 0; g < G && ok; ++g) {
+        gr[g].i0 = n * g / G;
+        gr[g].n = n * (g + 1) / G - gr[g].i0;
+        gr[g].fb = alloc_fan(sg, 2 * gr[g].n);
+        gr[g].st = g == 0 ? st : ctx->pipe[g - 1];
+        gr[g].iters = 0;
+        ok = sg.err == cudaSuccess && gr[g].fb.exit_out;
     }
-    if (active > 0) return fail(ctx, RTB_ERR_ARG, "rtb_shoot_refine: bracket too wide (no convergence in 4096 iterations)");
-    refine_final_fill_kernel<<<g, 256, 0, st>>>(d_a, d_b, d_msz, Tn, n, d_theta, fb);
-    if ((rc = launch_fan(ctx, p, fb, n, M))) return rc;
-    refine_result_kernel<<<g, 256, 0, st>>>(d_tx, d_ty, Tn, n, fb, d_res);
+    if (!ok) return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_refine: staging", sg.err);
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(st);
+        for (auto &ps : ctx->pipe) cudaStreamSynchronize(ps);
+        return code;
+    };
+    CK(cudaMemsetAsync(ctx->d_total, 0, 2 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long) * 2 * G, st));
+    CK(cudaEventRecord(ctx->ev[1], st));
+    int64_t launches = 0;
+    for (int g = 0; g < G; ++g) {
+        const Group &k = gr[g];
+        refine_init_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, st>>>(d_lo, d_hi, d_steps, d_msz, Tn, k.i0, k.n, q->src_x,
+                                                                       q->src_y, d_a, d_b, k.fb, d_active + 2 * g);
+        ++launches;
+    }
+    std::vector<unsigned long long> h_active(2 * G);
+    CK(cudaMemcpyAsync(h_active.data(), d_active, sizeof(unsigned long long) * 2 * G, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    int64_t iters = 0;
+    for (int g = 0; g < G; ++g) {
+        if (h_active[2 * g] == 0) continue;
+        double w;
+        std::memcpy(&w, &h_active[2 * g + 1], sizeof(w)); // widest |c - d| of the group
+        // passes until |c - d| * GOLD_RATIO^k <= GOLD_TOL, + 1: the rounding of the bracket arithmetic can delay the
+        // last pass of a pair by one (a pair that has converged takes no steps, so the spare pass costs nothing)
+        int k = 0;
+        while (w > RTB_GOLD_TOL && k < 4096) { w *= RTB_GOLD_RATIO; ++k; }
+        gr[g].iters = k + 1;
+        iters = std::max<int64_t>(iters, k);
+    }
+    // fork: the side streams start after the brackets are initialised
+    CK(cudaEventRecord(ctx->pipe_ev[0], st));
+    for (int g = 1; g < G; ++g) CK(cudaStreamWaitEvent(gr[g].st, ctx->pipe_ev[0], 0));
+    CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long) * 2 * G, st));
+    int max_it = 0;
+    for (auto &k : gr) max_it = std::max(max_it, k.iters);
+    // golden's while loop (RT:188): every pass re-traces both probes of every still-active pair; the groups' passes
+    // are enqueued round-robin so that the device always has several independent launches to interleave
+    for (int it = 0; it < max_it; ++it) {
+        for (int g = 0; g < G; ++g) {
+            const Group &k = gr[g];
+            if (it >= k.iters) continue;
+            if ((rc = launch_fan(ctx, p, k.fb, 2 * k.n, M, k.st))) return bail(rc);
+            refine_update_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, k.st>>>(d_tx, d_ty, Tn, k.i0, k.n, d_a, d_b, k.fb,
+                                                                               d_active + 2 * g + (it == k.iters - 1 ? 0 : 1)); // [2g]: pairs left after the last pass; [2g+1]: sink
+            launches += 2;
+        }
+    }
+    // join
+    for (int g = 1; g < G; ++g) {
+        CK(cudaEventRecord(ctx->pipe_ev[g], gr[g].st));
+        CK(cudaStreamWaitEvent(st, ctx->pipe_ev[g], 0));
+    }
+    CK(cudaMemcpyAsync(h_active.data(), d_active, sizeof(unsigned long long) * 2 * G, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (int g = 0; g < G; ++g)
+        if (h_active[2 * g] != 0)
+            return fail(ctx, RTB_ERR_ARG, "rtb_shoot_refine: golden did not converge in the predicted number of passes");
+    const unsigned gn = (unsigned)((n + 255) / 256);
+    FanBuffers fb = alloc_fan(sg, n); // the final re-trace of theta* = (a+b)/2, all pairs in one launch
+    if (sg.err != cudaSuccess || !fb.exit_out) return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_refine: staging", sg.err);
+    refine_final_fill_kernel<<<gn, 256, 0, st>>>(d_a, d_b, d_steps, d_msz, Tn, n, q->src_x, q->src_y, d_theta, fb);
+    if ((rc = launch_fan(ctx, p, fb, n, M))) return bail(rc);
+    refine_result_kernel<<<gn, 256, 0, st>>>(d_tx, d_ty, Tn, n, fb, d_res);
     launches += 3;
     CK(cudaGetLastError());
     CK(cudaEventRecord(ctx->ev[2], st));

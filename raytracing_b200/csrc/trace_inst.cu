@@ -10,9 +10,8 @@
 #define RTB_CAT(a, b) RTB_CAT2(a, b)
 
 namespace rtb {
-cudaError_t RTB_CAT(launch_trace_m, RTB_METHOD)(const TraceArgs &a, bool iso, bool traj, bool exact, int block,
-                                                cudaStream_t st)
+cudaError_t RTB_CAT(launch_trace_m, RTB_METHOD)(const TraceArgs &a, const LaunchCfg &c, cudaStream_t st)
 {
-    return launch_trace<RTB_METHOD>(a, iso, traj, exact, block, st);
+    return launch_trace<RTB_METHOD>(a, c, st);
 }
 } // namespace rtb

@@ -62,18 +62,21 @@ __device__ double pchip_eval(const Col &T, const Col &Y, int i, int n, double ta
 }
 
 // out (4, nt, R): x, y, angle, valid (1 / 0)
-__global__ void wavefront_kernel(const double *s_ray, const double *d_ray, int64_t R, const double *times, int nt,
-                                 double *out)
+__global__ void wavefront_kernel(const double *s_ray, const double *d_ray, int64_t rows, int64_t R, const double *times,
+                                 int nt, double *out)
 {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y;
     if (r >= R) return;
-    const int n = (int)d_ray[2 * R + r] + 1; // rows 0..d_ray[2]
+    // rows 0..d_ray[2]; never past the array (a strided or truncated s_ray has fewer rows than d_ray[2] + 1: the
+    // input must be the stride-1 trajectory, rtb_wavefront rejects anything else it can detect)
+    const int n = (int)min((int64_t)d_ray[2 * R + r] + 1, rows);
     const size_t stride = (size_t)6 * R;
     const Col T = {s_ray + 4 * R + r, stride};
     const double tau = times[j];
     double x = 0, y = 0, ang = 0, valid = 0;
-    if (n >= 2 && T[n - 1] >= tau && tau >= T[0]) { // np.max(t_ray) >= travel_time (T is increasing from 0)
+    if (n >= 2 && T[n - 1] >= tau) { // np.max(t_ray) >= travel_time, the reference's only test (RT:995; T increases
+                                     // from 0, a tau below T[0] extrapolates the first interval like PchipInterpolator)
         int lo = 0, hi = n - 1; // largest i with T[i] <= tau, clamped to n-2 (PPoly interval rule)
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
@@ -102,7 +105,7 @@ extern "C" int rtb_wavefront(rtb_ctx *ctx, int32_t ptr_kind, const double *s_ray
     const double *ds = sg.in(s_ray, (size_t)rows * 6 * R), *dd = sg.in(d_ray, (size_t)3 * R), *dt = sg.in(times, (size_t)nt);
     double *dout = sg.out(out, (size_t)4 * nt * R);
     if (sg.err != cudaSuccess) return fail(ctx, RTB_ERR_NOMEM, "rtb_wavefront: staging", sg.err);
-    wavefront_kernel<<<dim3((unsigned)((R + 127) / 128), (unsigned)nt), 128, 0, ctx->stream>>>(ds, dd, R, dt, nt, dout);
+    wavefront_kernel<<<dim3((unsigned)((R + 127) / 128), (unsigned)nt), 128, 0, ctx->stream>>>(ds, dd, rows, R, dt, nt, dout);
     CK(cudaGetLastError());
     sg.copy_back();
     CK(cudaStreamSynchronize(ctx->stream));

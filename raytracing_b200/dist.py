@@ -53,13 +53,22 @@ class FusedGather:
     (CUDA IPC between the per-GPU processes), so no all-gather follows the kernel -- ranks only agree that they are
     done (`finish`: a one-element all-reduce).  Same bytes as `gather_rays(d_ray)`.
 
+    Shards are contiguous (`offset` = this rank's first ray) or block-cyclic (`cyclic_block` = the block of
+    `cyclic_indices`, a power of two: local ray r is global ray ((r // block) * world + rank) * block + r % block).
+
+    The arrays are DOUBLE-BUFFERED: trace k writes set k % 2 on every GPU, so a rank that races ahead into trace k+1
+    stores into the other set while slower ranks still read the view `finish` gave them for trace k; it cannot reach
+    trace k+2 (which reuses set k % 2) before every rank has entered finish() of trace k+1, i.e. -- stream order --
+    after every rank's work on view k queued before its trace k+1.  Consumers must therefore use a view (on the
+    engine's stream) before they launch the next trace but one.
+
         fg = FusedGather(engine, R_total, lo, group)      # collective: exchanges IPC handles
         engine.trace(...device tensors of rays lo..hi...) # writes every peer
-        d_ray_all = fg.finish()                           # torch view (3, R_total) of this rank's copy
+        d_ray_all = fg.finish()                           # torch view (3, R_total) of this rank's copy of this trace
         fg.close()                                        # collective
     """
 
-    def __init__(self, engine, R_total, offset, group=None):
+    def __init__(self, engine, R_total, offset=0, group=None, cyclic_block=None):
         import torch
         import torch.distributed as dist
         self.engine, self.group, self.R = engine, group, int(R_total)
@@ -67,41 +76,59 @@ class FusedGather:
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         if self.world > 8:
             raise ValueError("FusedGather: at most 8 GPUs (one node)")
+        self.offset, self.cyclic_block = int(offset), cyclic_block
         self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", engine.device))
-        self.own, self.bases, err = None, [], None
+        self.own, self.bases, err = [None, None], [[], []], None
+        handles_mine = [None, None]
         try:
-            self.own, handle = engine.gather_alloc(3 * 8 * self.R)
+            for b in range(2):
+                self.own[b], handles_mine[b] = engine.gather_alloc(3 * 8 * self.R)
         except Exception as e:  # the outcome is agreed on below: no rank may leave the others in a collective
-            handle, err = None, e
+            handles_mine, err = None, e
         handles = [None] * self.world
-        dist.all_gather_object(handles, handle, group=group)
+        dist.all_gather_object(handles, handles_mine, group=group)
         if err is None and all(h is not None for h in handles):
             try:
-                self.bases = [self.own if r == self.rank else engine.gather_open(handles[r]) for r in range(self.world)]
+                for b in range(2):
+                    self.bases[b] = [self.own[b] if r == self.rank else engine.gather_open(handles[r][b])
+                                     for r in range(self.world)]
             except Exception as e:
                 err = e
-        ok = torch.tensor([0 if err is not None or not self.bases else 1], dtype=torch.int32, device=self._flag.device)
+        ok = torch.tensor([0 if err is not None or not self.bases[1] else 1], dtype=torch.int32, device=self._flag.device)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
         if int(ok.item()) == 0:     # some rank could not allocate / map (no peer access): nobody uses the fused path
             self._release()
             raise RuntimeError("FusedGather: peer mapping unavailable on at least one rank (%s)" % (err,))
-        engine.set_gather(self.bases, self.R, offset)
-        self.view = torch.as_tensor(_DevArray(self.own, self.R), device=self._flag.device)
-        dist.barrier(group=group)      # every peer has mapped this buffer before anyone traces
+        self.views = [torch.as_tensor(_DevArray(self.own[b], self.R), device=self._flag.device) for b in range(2)]
+        self._cur = 0
+        self._arm()
+        dist.barrier(group=group)      # every peer has mapped these buffers before anyone traces
+
+    def _arm(self):
+        """Point the engine's next trace at buffer set self._cur."""
+        if self.cyclic_block:
+            self.engine.set_gather_cyclic(self.bases[self._cur], self.R, self.cyclic_block, self.world, self.rank)
+        else:
+            self.engine.set_gather(self.bases[self._cur], self.R, self.offset)
 
     def _release(self):
-        for r, b in enumerate(self.bases):
-            if r != self.rank:
-                self.engine.gather_close(b, own=False)
-        if self.own is not None:
-            self.engine.gather_close(self.own, own=True)
-        self.bases, self.own = [], None
+        for b in range(2):
+            for r, p in enumerate(self.bases[b]):
+                if r != self.rank:
+                    self.engine.gather_close(p, own=False)
+            if self.own[b] is not None:
+                self.engine.gather_close(self.own[b], own=True)
+        self.bases, self.own = [[], []], [None, None]
 
     def finish(self):
-        """All ranks' kernels have completed (stream-ordered after this rank's own): the local array is whole."""
+        """All ranks' kernels of this trace have completed (stream-ordered after this rank's own): the local array
+        is whole.  Returns its view and points the next trace at the other buffer set."""
         import torch.distributed as dist
         dist.all_reduce(self._flag, group=self.group)
-        return self.view
+        view = self.views[self._cur]
+        self._cur ^= 1
+        self._arm()
+        return view
 
     def close(self):
         import torch

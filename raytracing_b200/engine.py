@@ -208,6 +208,45 @@ class Engine:
         arr = (C.c_void_p * max(n, 1))(*[C.c_void_p(b) for b in (bases or [])])
         self._check(self._lib.rtb_set_gather(self._ctx, n, arr, int(R_total), int(offset)))
 
+    def set_gather_cyclic(self, bases, R_total, block, nranks, rank):
+        """set_gather for block-cyclic shards (dist.cyclic_indices): local ray r is global ray
+        ((r // block) * nranks + rank) * block + r % block."""
+        arr = (C.c_void_p * len(bases))(*[C.c_void_p(b) for b in bases])
+        self._check(self._lib.rtb_set_gather_cyclic(self._ctx, len(bases), arr, int(R_total), int(block), int(nranks),
+                                                    int(rank)))
+
+    def set_option(self, name, value):
+        """Tuning / test switches (include/rtb.h rtb_set_option): "queue" 0 auto | 1 always | 2 never (static grid);
+        "traj_store" 0 auto (staged rows + TMA stores) | 1 per-lane stores."""
+        opt = {"queue": _cabi.RTB_OPT_QUEUE, "traj_store": _cabi.RTB_OPT_TRAJ_STORE}[name]
+        self._check(self._lib.rtb_set_option(self._ctx, opt, int(value)))
+
+    def build_id(self):
+        return self._lib.rtb_build_id().decode()
+
+    def sweep(self, method, theta0, x0, y0, steps, max_sizes, gamma, box, metric, skip_lo=0, skip_hi=0, exact=False):
+        """rtb_sweep: the DELTA_S sweep (RT_bench.py:1303-1318) as batched traces of candidates x rays with the
+        per-candidate reductions on the device.  metric: "snell" | "closure" | "px_cv".  numpy in, numpy out:
+        (sum[C], max[C], count[C], stats)."""
+        theta0 = np.ascontiguousarray(theta0, dtype=np.float64).ravel()
+        R = theta0.size
+        x0 = np.ascontiguousarray(np.broadcast_to(np.asarray(x0, dtype=np.float64), (R,)))
+        y0 = np.ascontiguousarray(np.broadcast_to(np.asarray(y0, dtype=np.float64), (R,)))
+        steps = np.ascontiguousarray(steps, dtype=np.float64)
+        max_sizes = np.ascontiguousarray(max_sizes, dtype=np.int64)
+        Cn = steps.size
+        assert max_sizes.size == Cn
+        sm, mx, cnt = np.zeros(Cn), np.zeros(Cn), np.zeros(Cn, dtype=np.int64)
+        mid = {"snell": _cabi.RTB_SWEEP_SNELL, "closure": _cabi.RTB_SWEEP_CLOSURE, "px_cv": _cabi.RTB_SWEEP_PX_CV}[metric]
+        flags = _cabi.RTB_F_EXACT_BASIS if exact else 0
+        p = _cabi.RtbParams(method_id(method), flags, _cabi.RTB_PTR_HOST, 1, 1, float(gamma), 0.0,
+                            float(box[0]), float(box[1]), float(box[2]), float(box[3]), None, None)
+        spec = _cabi.RtbSweepSpec(steps.ctypes.data, max_sizes.ctypes.data, Cn, mid, int(skip_lo), int(skip_hi))
+        stats = _cabi.RtbStats()
+        self._check(self._lib.rtb_sweep(self._ctx, C.byref(p), theta0.ctypes.data, x0.ctypes.data, y0.ctypes.data, R,
+                                        C.byref(spec), sm.ctypes.data, mx.ctypes.data, cnt.ctypes.data, C.byref(stats)))
+        return sm, mx, cnt, self._stats(stats)
+
     def fp64_peak(self):
         v = C.c_double()
         self._check(self._lib.rtb_fp64_peak(self._ctx, C.byref(v)))
@@ -225,7 +264,7 @@ class Engine:
 
     def trace(self, method, theta0, x0, y0, step, max_size, gamma, box, interface=False, full=True,
               out_stride=1, want_last_row=True, want_px_stats=False, want_errors=None, exact=False,
-              steps=None, max_sizes=None, out=None, tail_zero=True):
+              steps=None, max_sizes=None, out=None, tail_zero=True, static_grid=False):
         """trazar's integration for an explicit fan.
 
         Inputs are numpy arrays (host pointers, staged inside the call) or torch CUDA tensors
@@ -263,7 +302,7 @@ class Engine:
         last_row = out.get("last_row", empty(6, R) if want_last_row else None)
         px_stats = out.get("px_stats", empty(3, R) if want_px_stats else None)
         flags = (_cabi.RTB_F_INTERFACE if interface else 0) | (_cabi.RTB_F_EXACT_BASIS if exact else 0) | \
-                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO)
+                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO) | (_cabi.RTB_F_STATIC_GRID if static_grid else 0)
         steps_a = max_sizes_a = None
         if steps is not None:
             if dev:
@@ -283,8 +322,7 @@ class Engine:
         self._check(self._lib.rtb_trace(self._ctx, C.byref(p), ptr(theta0), ptr(x0), ptr(y0), R, ptr(s_ray),
                                         ptr(d_ray), ptr(errors), ptr(last_row), ptr(px_stats), C.byref(stats)))
         return TraceResult(s_ray=s_ray, d_ray=d_ray, errors=errors, last_row=last_row, px_stats=px_stats,
-                           stats=dict(kernel_ms=stats.kernel_ms, total_ms=stats.total_ms, ray_steps=stats.ray_steps,
-                                      launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes))
+                           stats=self._stats(stats))
 
     # -- batched two-point shooting search (include/rtb.h rtb_shoot_*; parity-unpinned) --
     def _shoot_args(self, method, src, steps, max_sizes, targets, gamma, box, exact, like):
@@ -316,7 +354,8 @@ class Engine:
     @staticmethod
     def _stats(stats):
         return dict(kernel_ms=stats.kernel_ms, total_ms=stats.total_ms, ray_steps=stats.ray_steps,
-                    launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes)
+                    launches=stats.launches, h2d_bytes=stats.h2d_bytes, d2h_bytes=stats.d2h_bytes,
+                    nonfinite_rays=stats.nonfinite_rays)
 
     def shoot_coarse(self, method, angles, src, steps, max_sizes, targets, gamma, box, index0=0, want_exit=False,
                      exact=False):

@@ -1,13 +1,15 @@
 """Generate the golden fixtures in tests/golden/ from the UNMODIFIED reference.
 
 Runs only in the build container (needs /root/reference); the fixtures are committed so the
-tests run anywhere.  Usage:  python tests/golden/gen_golden.py [traj|field|sweep|sens|shoot|all]
+tests run anywhere.  Usage:  python tests/golden/gen_golden.py [traj|field|sweep|sens|shoot|edge|bench|all]
 
   ref_traj.npz    trazar outputs of every (scenario, method) on the default fans (d_ray, errors,
                   strided s_ray rows, last row per ray) and on slices of the synthetic fans
   ref_field.npz   n_gradient at random points and next to knots, per scenario
   ref_sweep.npz   search_delta metrics over the DELTA_S sweep + find_index result (RT:1303-1385)
   ref_shoot.npz   two-point shooting problems solved with RT.trazar rays + RT.golden refinement
+  ref_edge.npz    rays leaving the box on their first / second step (op7's bootstrap steps carry no box test)
+  ref_bench.npz   remove_outliers_iqr + the median-of-last-30 % / 0.5 % loop of the benchmark mode on recorded samples
   sensitivity.json  the reference algorithm's response to +-1 ulp sin/cos noise (oracle probe,
                   cross-checked against the same probe on the real reference for a few cases)
 """
@@ -216,6 +218,54 @@ def gen_shoot():
     np.savez_compressed(os.path.join(HERE, "ref_shoot.npz"), **flat)
 
 
+def gen_edge():
+    """ref_edge.npz: rays that leave the box on their first or second step.  op7 takes its two bootstrap steps
+    before the loop that holds the box test (RT:838-866), so such a ray still reaches row 3; every other method
+    breaks at once (RT:878)."""
+    flat = {}
+    theta = np.array([np.pi, np.pi, 2.8, -2.5, 0.3])
+    pos_x = np.array([-2.0, -1.996, -2.0, -1.996, -2.0])
+    for m in (7, 6, 1):
+        RT = L.load_reference()
+        z, grd = L.setup_scenario(RT, "3", dict(theta_v=theta, pos_x=pos_x, ray_count=len(theta)))
+        s, d, _ct, _e = RT.trazar(L.method(RT, m), z, grd, False, RT.DELTA_S, RT.DELTA_S_DIVISOR_FISHEYE + 1, "3")
+        flat["s3_op%d/d_ray" % m] = d
+        flat["s3_op%d/rows" % m] = s[:8].copy()
+        print("edge op%d" % m, d[2], flush=True)
+    flat["theta"] = theta
+    flat["pos_x"] = pos_x
+    np.savez_compressed(os.path.join(HERE, "ref_edge.npz"), **flat)
+
+
+def gen_bench():
+    """ref_bench.npz: the benchmark statistic of RT:1516-1538 on recorded sample streams.  remove_outliers_iqr is the
+    reference's own function (RT:123-138); the loop around it lives inline in main() (it spawns worker processes and
+    reads input()), so its four statistic statements are replayed here verbatim on the recorded samples."""
+    RT = L.load_reference()
+    flat = {}
+    for case, (seed, n, drift) in enumerate(((1, 300, 0.0), (2, 200, 0.02), (3, 400, 0.004))):
+        rng = np.random.default_rng(seed)
+        rounds, benchmarks = [], []
+        while True:
+            base = 1.0 + drift / (1 + len(rounds))                 # rounds settle like a warming-up machine
+            arr = base + 0.01 * rng.standard_normal(n)
+            arr[rng.integers(0, n, 7)] += rng.uniform(0.2, 3.0, 7)  # outliers for the IQR filter
+            rounds.append(arr.copy())
+            cleaned_arr = RT.remove_outliers_iqr(arr)                                   # RT:1530
+            new_size = len(cleaned_arr)                                                 # RT:1531
+            benchmarks.append(np.median(cleaned_arr[int(-0.3 * new_size):]))            # RT:1532
+            if len(benchmarks) >= 2:                                                    # RT:1534-1537
+                diff_percent = 100 * abs(benchmarks[-1] - benchmarks[-2]) / max(benchmarks[-1], benchmarks[-2])
+                if diff_percent < 0.5:
+                    break
+        flat["case%d/samples" % case] = np.stack(rounds)
+        flat["case%d/benchmarks" % case] = np.array(benchmarks)
+        flat["case%d/final" % case] = np.float64(np.mean(benchmarks[-2:]))              # RT:1539
+        flat["case%d/cleaned0" % case] = RT.remove_outliers_iqr(rounds[0])
+        print("bench case", case, len(rounds), "rounds ->", flat["case%d/final" % case], flush=True)
+    np.savez_compressed(os.path.join(HERE, "ref_bench.npz"), **flat)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("sens", "all"):
@@ -228,3 +278,7 @@ if __name__ == "__main__":
         gen_sweep()
     if what in ("shoot", "all"):
         gen_shoot()
+    if what in ("edge", "all"):
+        gen_edge()
+    if what in ("bench", "all"):
+        gen_bench()

@@ -82,6 +82,22 @@ def test_benchmark_statistic():
     assert abs(api.benchmark_statistic(lambda: next(seq), trial=20) - 1.0) < 0.02
 
 
+def test_benchmark_statistic_vs_reference_vectors():
+    """ref_bench.npz (gen_golden.py bench): the reference's remove_outliers_iqr (RT:123-138) and its
+    median-of-the-last-30 % / 0.5 % loop (RT:1516-1539) on recorded sample streams."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "ref_bench.npz"))
+    for case in range(3):
+        samples = g["case%d/samples" % case]
+        assert np.array_equal(api.remove_outliers_iqr(samples[0]), g["case%d/cleaned0" % case])
+        stream = iter(samples.ravel())
+        got = api.benchmark_statistic(lambda: next(stream), trial=samples.shape[1], replicas=1)
+        assert got == float(g["case%d/final" % case])          # same statements, same numpy: bit-exact
+        with pytest.raises(StopIteration):                       # ... after exactly as many rounds as the reference
+            next(stream)
+
+
 def test_make_fan_sharding_consistent():
     full = rt.make_fan("2", 1 << 12)
     part = rt.make_fan("2", 1 << 12, 1000, 1100)

@@ -59,3 +59,20 @@ def test_fingerprints_baseline_md(golden_traj):
             "default_s3_op6": 56567, "default_s3_op7": 56571, "default_s4_op10": 60457, "default_s4_op11": 60457}
     for k, v in want.items():
         assert int(golden_traj[k + "/d_ray"][2].sum()) == v
+
+
+def test_rays_leaving_on_their_first_steps_vs_reference():
+    """ref_edge.npz (gen_golden.py edge): op7 takes its two bootstrap steps before the loop that holds the box test
+    (RT:838-866), so a ray that is outside after step 1 or 2 still reaches row 3; op6/op1 break at once (RT:878)."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "ref_edge.npz"))
+    s = scenario_setup("3")
+    theta, pos_x = g["theta"], g["pos_x"]
+    for m in (7, 6, 1):
+        o = O.trace(m, s["z"], s["grd"], s["step"], s["M"], s["gamma"], s["box"], False, theta, pos_x, np.full(theta.size, -2.0))
+        d = g["s3_op%d/d_ray" % m]
+        assert np.array_equal(o["d_ray"][2], d[2]), m
+        assert_close(o["d_ray"][:2], d[:2], 1e-10, "edge d_ray op%d" % m)
+        assert_close(o["s_ray"][:8], g["s3_op%d/rows" % m], 1e-10, "edge rows op%d" % m)
+    assert list(g["s3_op7/d_ray"][2][:4]) == [3, 3, 3, 3] and list(g["s3_op6/d_ray"][2][:4]) == [1, 2, 1, 2]

@@ -24,8 +24,10 @@ for f in funcs[1:]:
         if m2:
             tgt = int(m2.group(1), 16)
             if tgt < a and tgt in addr_idx and any(addr_idx[tgt] <= v <= k for v in vote):
-                if best is None or (k - addr_idx[tgt]) > (best[1] - best[0]):
-                    best = (addr_idx[tgt], k)
+                # the step loop = the backward-branch region (holding a VOTE) with the most FP64 arithmetic
+                nd = sum(1 for _, tt in ins[addr_idx[tgt]:k + 1] if re.search(r"\bD(FMA|MUL|ADD)\b", tt))
+                if best is None or nd > best[2]:
+                    best = (addr_idx[tgt], k, nd)
     if not best:
         print(name, "no loop found"); continue
     body = ins[best[0]:best[1] + 1]
