@@ -166,6 +166,13 @@ static void second_order_taylor(double x, double y, double ux, double uy, double
     *fy = (y + uy * step) + (gy - dot * uy) * s2 / (2.0 * n0);
 }
 
+/* Second sensitivity probe (test infrastructure): curvature_t switches between a straight step that keeps the angle and
+ * an arc at curv < GOLD_TOL (RT:349).  A ray whose curvature sits on that threshold takes one branch or the other
+ * depending on the last bits of curv; scaling the threshold by 1 +- 1e-14 shows which rays those are. */
+static double g_curv_tol_scale = 1.0;
+void rto_set_curv_tol_scale(double s) { g_curv_tol_scale = s; }
+
+
 /* curvature_t RT:335-365; returns `ignore` */
 static int curvature_t(double ang, double gx, double gy, double ux, double uy, double n0, double x,
                        double y, double step, double gold_tol, double *fx, double *fy)
@@ -173,7 +180,7 @@ static int curvature_t(double ang, double gx, double gy, double ux, double uy, d
     double dot = gx * ux + gy * uy;
     double qx = gx - dot * ux, qy = gy - dot * uy;
     double curv = sqrt(qx * qx + qy * qy) / n0;
-    if (curv < gold_tol) {
+    if (curv < gold_tol * g_curv_tol_scale) { /* scale == 1 unless the threshold probe is on (rto_set_curv_tol_scale) */
         *fx = x + ux * step;
         *fy = y + uy * step;
         return 0;

@@ -47,6 +47,8 @@ def lib():
         _lib.rto_max_threads.restype = C.c_int
         _lib.rto_set_trig_noise.restype = None
         _lib.rto_set_trig_noise.argtypes = [C.c_int]
+        _lib.rto_set_curv_tol_scale.restype = None
+        _lib.rto_set_curv_tol_scale.argtypes = [C.c_double]
     return _lib
 
 
@@ -120,3 +122,9 @@ def set_trig_noise(seed):
     """0 = off (faithful oracle); >0 = every sin/cos result moved by +-1 ulp with probability 1/2
     (sensitivity probe of the reference algorithm, see rt_oracle.c)."""
     lib().rto_set_trig_noise(int(seed))
+
+
+def set_curv_tol_scale(scale):
+    """1.0 = faithful oracle; 1 +- 1e-14 = probe of curvature_t's GOLD_TOL switch (RT:349): shows the rays whose
+    curvature sits on the threshold, where the last bits of the curvature pick the branch (see rt_oracle.c)."""
+    lib().rto_set_curv_tol_scale(float(scale))

@@ -56,7 +56,8 @@ def results_metric(uc, s_ray, errors):
     return np.mean([px_cv(s_ray[:, 2, i]) for i in range(1, R - 1)])
 
 
-def print_results(uc, metric, out=sys.stdout):
+def print_results(uc, metric, out=None):
+    out = out or sys.stdout
     print("\nRESULTS", file=out)
     if uc == "2":
         print("Closure error ", metric, "%", file=out)
@@ -66,9 +67,10 @@ def print_results(uc, metric, out=sys.stdout):
         print("Average ray Coefficient of Variation: ", metric, file=out)
 
 
-def run(scenario, method_choice, delta_s="default", benchmark=False, trials=100, show=True, out=sys.stdout, device=0,
+def run(scenario, method_choice, delta_s="default", benchmark=False, trials=100, show=True, out=None, device=0,
         fit="device"):
     """One pass through the reference's main(): returns a dict with everything printed."""
+    out = out or sys.stdout
     uc = SCENARIOS.get(str(scenario), str(scenario))
     uc = K.scenario_id(uc)
     m = menu_to_method(uc, method_choice)

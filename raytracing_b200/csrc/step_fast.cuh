@@ -46,107 +46,178 @@ struct CostIsoFast {
 };
 
 struct CostAnisoFast {
-    double n1, gamma, g2m1, mx, my, gx1h, gy1h; // mx = mi_x + h*coef_i*gx0/2 ; gx1h = h*gx1/2
+    double n1, n1g2, g2m1, mx, my, gx1h, gy1h; // n1g2 = n1 gamma^2; mx = mi_x + h*coef_i*gx0/2 ; gx1h = h*gx1/2
     __device__ __forceinline__ double operator()(double s, double c) const
     {
-        // anisotropy^2 = gamma^2 s^2 + c^2 = 1 + (gamma^2 - 1) s^2 =: v, coef = sqrt(v) = v y with y = 1/sqrt(v), and
-        // coef (1 - s^2 k) = coef - w s^2, coef (1 + c^2 k) = coef + w c^2 with k = (gamma^2 - 1)/v, w = (gamma^2 - 1) y
-        const double s2 = s * s, c2 = c * c;
-        const double v = fma(g2m1, s2, 1.0);
+        // anisotropy^2 = gamma^2 s^2 + c^2 = 1 + (gamma^2 - 1) s^2 =: v, coef = sqrt(v) = v y with y = 1/sqrt(v).
+        // The momentum of RT:217-230 simplifies exactly: p_x = n coef c (1 - s^2 (gamma^2-1)/v) = n c y (the bracket is
+        // 1/v), p_y = n coef s (1 + c^2 (gamma^2-1)/v) = n gamma^2 s y (v + (gamma^2-1) c^2 = gamma^2): the probe's
+        // momentum lies on the ellipse p_x^2 + p_y^2 / gamma^2 = n^2.
+        const double v = fma(g2m1, s * s, 1.0);
         double y; // MUFU seed + one cubically convergent step
         asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
         const double e = fma(-v * y, y, 1.0);
         y = fma(y, fma(e, 0.375, 0.5) * e, y);
-        const double coef = v * y, w = g2m1 * y;
-        const double a = fma(n1 * c, fma(-w, s2, coef), -fma(coef, gx1h, mx));
-        const double b = fma(n1 * s, fma(w, c2, coef), -fma(coef, gy1h, my));
+        const double coef = v * y;
+        const double a = fma(n1, c * y, -fma(coef, gx1h, mx));
+        const double b = fma(n1g2, s * y, -fma(coef, gy1h, my));
         return fma(a, a, b * b);
     }
 };
 
-// golden (RT:175-199) with the trigonometry of the probes done by angle addition.
+// ------------------------------------------------------------------------------------------------------------------
+// golden (RT:175-199) without its bracket arithmetic.
 //
-// The bracket, the probe angles c, d and every comparison are computed exactly as the reference does (same
-// floating-point expressions, same `while abs(c-d) > tol`, same `if f(c) < f(d)`, result (a+b)/2).  What changes is
-// how sin/cos of a probe is obtained: every call starts from [theta - pi/2, theta + pi/2], so the probe created in
-// iteration k sits at the kept probe -+ pi*rho^(k+4) -- constants (golden_table.cuh) -- plus the rounding of the
-// reference's own expressions, which is measured (eps) and applied to first order.  sin/cos(theta) come from the ray
-// state.  The kept probe keeps its cost value (the reference re-evaluates it at an angle that differs by rounding
-// only: the costs are sums of squares of small residuals, so a change of ~1e-16 in the angle moves them by ~1e-20,
-// far below the ~1e-16 differences the comparisons decide on).  One cost evaluation and ~20 FP64 instructions per
-// iteration instead of two evaluations with a full sincos each.
-// Near-ties -- |f(c) - f(d)| within ~16 ulp-level perturbations of the residuals, i.e. (f(c)-f(d))^2 <=
-// (3.6e-15 * scale)^2 * max f with f = |residual|^2 and scale = the size of the terms the residual is the
-// difference of -- are where the rounding of *any* evaluation decides (among them the exact tie of a ray running
-// along grad n).  They are re-decided with both probes evaluated afresh at the reference's probe angles with a
-// full-accuracy sincos (no cached value, no angle-addition chain); a few per cent of the last iterations.
-// Returns (a+b)/2 and its sin/cos.
-template <class F, class FX>
-__device__ __forceinline__ double golden_trig(const F &cost, const FX &exact_less, double scale, double theta, double st,
+// Every call starts from [theta - pi/2, theta + pi/2] (DELTA_G, RT:64) and shrinks the bracket by GOLD_RATIO per pass
+// whatever the cost does, so (i) the loop `while abs(c-d) > GOLD_TOL` runs exactly RTB_GOLDEN_ITERS = 37 times,
+// (ii) relative to theta every bracket end, probe and midpoint is a sum of +- constants picked by the decisions
+// `f(c) < f(d)` taken so far.  The searches below therefore carry only what a decision needs -- the kept and the new
+// probe's (sin, cos, cost), or for the symmetric cost just the signed distance of the bracket midpoint from the
+// minimum -- plus the decision bits; a, b, c, d themselves are never formed.  The returned angle theta + (sum of the
+// midpoint moves) differs from the reference's (a+b)/2 by the rounding of its bracket arithmetic (< 1e-15).
+//
+// Near-ties are where the rounding of *any* evaluation decides (among them the exact tie of a ray running along
+// grad n): |f(c) - f(d)| within ~16 ulp-level perturbations of the residuals.  They are decided the reference's way,
+// out of line: the probes c, d of that pass are rebuilt from the decision bits with the reference's own un-fused
+// expressions (golden_probes_at), and both costs are evaluated afresh in the reference's expression order (CostIso /
+// CostAniso of step.cuh) with libdevice's sincos -- no cached value, no angle-addition chain.  About one step in a
+// thousand per warp on the benchmark fans (ncu source counters, profiles/).
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef RTB_TIE_FLOOR
+#define RTB_TIE_FLOOR 2.0e-14 // covers the rounding drift of the reference's own a, b (37 passes x ulp(theta +- pi/2))
+#endif
+
+static __device__ __noinline__ double2 golden_probes_at(double theta, unsigned long long bits, int k)
+{
+    double a = __dsub_rn(theta, RTB_DELTA_G), b = __dadd_rn(theta, RTB_DELTA_G);
+    double c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    double d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    for (int j = 0; j < k; ++j) {
+        if ((bits >> j) & 1ull) b = d; else a = c; // RT:189-192
+        c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+        d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    }
+    return make_double2(c, d);
+}
+
+// What a near-tie needs to rebuild the reference's cost lambda: the step's inputs as they sit in registers anyway
+// (nothing is computed for it unless a tie occurs).
+struct TieIso { // RT:595,697
+    double n0, ux, uy, gx0, gy0, n1, gx1, gy1, h;
+    __device__ __forceinline__ CostIso make() const
+    {
+        CostIso cf;
+        cf.n1 = n1;
+        cf.n0ux = n0 * ux; cf.n0uy = n0 * uy;
+        cf.ix = h * (gx0 + gx1) / 2.0; cf.iy = h * (gy0 + gy1) / 2.0;
+        return cf;
+    }
+};
+struct TieAniso { // RT:725-729, 758-762
+    double n0, coef0, ux, uy, gx0, gy0, n1, gx1, gy1, h, gamma, g2m1;
+    __device__ __forceinline__ CostAniso make() const
+    {
+        CostAniso cf;
+        cf.n1 = n1; cf.gamma = gamma; cf.g2m1 = g2m1; cf.step = h;
+        cf.mi_x = moment_c(n0, coef0, g2m1, ux, -(uy * uy));
+        cf.mi_y = moment_c(n0, coef0, g2m1, uy, ux * ux);
+        cf.cgx0 = coef0 * gx0; cf.cgy0 = coef0 * gy0;
+        cf.gx1 = gx1; cf.gy1 = gy1;
+        return cf;
+    }
+};
+
+template <class TIE>
+static __device__ __noinline__ bool golden_tie(const TIE t, double theta, unsigned long long bits, int k)
+{
+    const double2 p = golden_probes_at(theta, bits, k);
+    const auto cf = t.make();
+    return cf(p.x) < cf(p.y); // RT:189
+}
+
+// Evaluating search (anisotropic cost; isotropic cost when the turn is too large for golden_iso_sym).  `cost(s, c)` is
+// the fast form of the cost, `ref` the reference-order functor used for near-ties, `scale` the size of the terms the
+// residual is the difference of.  The probe created in pass k sits at the kept probe -+ pi rho^(k+4) (kGoldenRot):
+// one rotation by table constants and one cost evaluation per pass; the kept probe keeps its cost.
+// Returns theta_new and its sin/cos.
+template <class F, class REF>
+__device__ __forceinline__ double golden_trig(const F &cost, const REF &ref, double scale, double theta, double st,
                                               double ct, double &s_out, double &c_out)
 {
     const double tie2 = (RTB_TIE_EPS * scale) * (RTB_TIE_EPS * scale);
-    double a = theta - RTB_DELTA_G, b = theta + RTB_DELTA_G;
-    double c = b - (b - a) * RTB_GOLD_RATIO;
-    double d = a + (b - a) * RTB_GOLD_RATIO;
-    const double S0 = kGolden0[0], C0 = kGolden0[1], P0 = kGolden0[2];
-    // left probe c = theta - P0 + rounding, right probe d = theta + P0 + rounding
-    double Lpsi = c - theta, Rpsi = d - theta;
-    double Ls = fma(-ct, S0, st * C0), Lc = fma(st, S0, ct * C0);
-    double Rs = fma(ct, S0, st * C0), Rc = fma(-st, S0, ct * C0);
-    {
-        const double el = Lpsi + P0, er = Rpsi - P0;
-        const double t0 = fma(Lc, el, Ls), t1 = fma(Rc, er, Rs);
-        Lc = fma(-Ls, el, Lc); Rc = fma(-Rs, er, Rc);
-        Ls = t0; Rs = t1;
-    }
-    // State of the loop: the kept probe W and the newest probe N (sin, cos, offset from theta, cost) and on which
-    // side N lies -- one conditional move of four doubles per iteration instead of shuffling a left and a right set.
-    double Ws = Ls, Wc = Lc, Wpsi = Lpsi, Wf = cost(Ls, Lc);
-    double Ns = Rs, Nc = Rc, Npsi = Rpsi, Nf = cost(Rs, Rc);
-    bool nl = false; // N is the left probe (c)
-    int k = 0;
+    const double S0 = kGolden0[0], C0 = kGolden0[1];
+    // the first probes: c = theta - P0 (left), d = theta + P0 (right)
+    double Ws = fma(-ct, S0, st * C0), Wc = fma(st, S0, ct * C0);   // kept probe W := c
+    double Ns = fma(ct, S0, st * C0), Nc = fma(-st, S0, ct * C0);   // newest probe N := d
+    double Wf = cost(Ws, Wc), Nf = cost(Ns, Nc);
+    bool nl = false;          // N is the left probe (c)
+    double m = 0.0;           // bracket midpoint - theta
+    unsigned long long bits = 0;
 #pragma unroll 1
-    while (fabs(c - d) > RTB_GOLD_TOL) {
-        bool left = nl ? (Nf < Wf) : (Wf < Nf); // RT:189: if func(c) < func(d): b = d  else: a = c
+    for (int k = 0; k < RTB_GOLDEN_ITERS; ++k) {
         const double df = Nf - Wf;
-        if (df * df <= tie2 * fmax(Nf, Wf)) left = exact_less(c, d);
-        if (left == nl) { Ws = Ns; Wc = Nc; Wpsi = Npsi; Wf = Nf; } // the kept probe: c when b moves, d when a moves
-        b = left ? d : b;
-        a = left ? a : c;
-        c = b - (b - a) * RTB_GOLD_RATIO;
-        d = a + (b - a) * RTB_GOLD_RATIO;
-        const int kk = min(k, RTB_GOLDEN_ROT_N - 1);
-        const double2 r = kGoldenRot[kk];
-        const double sgn = left ? -1.0 : 1.0; // the new probe lies left of the kept one when b moved
-        Npsi = (left ? c : d) - theta;
-        const double sr = sgn * r.x;
-        const double ns = fma(Wc, sr, Ws * r.y), nc = fma(-Ws, sr, Wc * r.y);
-        const double eps = Npsi - fma(sgn, kGoldenDelta[kk], Wpsi);
-        Ns = fma(nc, eps, ns); Nc = fma(-ns, eps, nc);
+        bool left = nl ? (df < 0.0) : (df > 0.0); // RT:189: if func(c) < func(d): b = d  else: a = c
+        if (df * df <= tie2 * fmax(Nf, Wf)) left = golden_tie(ref, theta, bits, k);
+        bits |= (unsigned long long)left << k;
+        if (left == nl) { Ws = Ns; Wc = Nc; Wf = Nf; } // the kept probe: c when b moves, d when a moves
+        const double q = kGoldenMid[k];
+        m += left ? -q : q;
+        const double2 r = kGoldenRot[k];
+        const double sr = left ? -r.x : r.x;      // the new probe lies left of the kept one when b moved
+        Ns = fma(Wc, sr, Ws * r.y);
+        Nc = fma(-Ws, sr, Wc * r.y);
         Nf = cost(Ns, Nc);
         nl = left;
-        ++k;
     }
-    const double th = (b + a) / 2.0;
-    // sin/cos of the result from the kept probe (|offset| <= final bracket ~3e-8: second order is exact to 1e-23)
-    const double e = (th - theta) - Wpsi, e2h = 0.5 * e * e;
+    // (a+b)/2 lies half a probe distance from the kept probe: to its left when the kept probe is d (N is c)
+    const double e = nl ? -RTB_GOLDEN_FINAL_HALF : RTB_GOLDEN_FINAL_HALF, e2h = 0.5 * e * e;
     s_out = fma(-Ws, e2h, fma(Wc, e, Ws));
     c_out = fma(-Wc, e2h, fma(-Ws, e, Wc));
-    return th;
+    return theta + m;
 }
 
-// golden (RT:175-199) for the isotropic cost without evaluating it: f(t) = |n1 (cos t, sin t) - A|^2 =
-// n1^2 + |A|^2 - 2 n1 |A| cos(t - ts) is symmetric about ts = arg A, so f(c) < f(d) <=> the midpoint of the probes
-// lies right of ts.  The bracket arithmetic (a, b, c, d, the loop test, the result (a+b)/2) is the reference's own;
-// each decision costs one addition and one comparison against ts = theta + delta, delta from the cross and dot
-// products of A with the ray direction.  Where the reference's computed f(c) - f(d) would be within its own rounding
-// noise -- |2 mu|^2 <= TIE^2 (D^2 / (|A|^2 q^2) + n1 / |A|), mu = midpoint - ts, q = half the probe distance (a
-// constant per iteration), D = n1 - |A|: the same criterion as golden_trig's, in the angle domain, taken twice as
-// wide -- both probes are evaluated like the reference does (exact_less).  Returns false when ts is more than 2^-6
-// from theta (a turn no step of the tested scenarios makes): the caller then runs golden_trig.
-template <class FX>
-__device__ __forceinline__ bool golden_iso_sym(double n1, double ax, double ay, const FX &exact_less, double theta,
+// Isotropic cost without evaluating it: f(t) = |n1 (cos t, sin t) - A|^2 = n1^2 + |A|^2 - 2 n1 |A| cos(t - ts) is
+// symmetric about ts = arg A, so f(c) < f(d) <=> the midpoint of the probes -- which is the bracket midpoint --
+// lies right of ts.  One signed distance e = midpoint - ts is carried; a pass subtracts copysign(kGoldenMid[k], e):
+// one integer sign transfer and one DADD, no comparison.  ts - theta comes from the cross and dot products of A with
+// the ray direction.  Where the reference's computed f(c) - f(d) would be within its own rounding noise --
+// |e| <= TIE/2 (|D| / (|A| q) + sqrt(n1 / |A|)) + floor, q = half the probe distance of the pass, D = n1 - |A|; tested
+// on the high words, a superset -- the search of that step is redone out of line by golden_sym_slow with the reference's
+// own bracket arithmetic, both probes of a pass inside the band evaluated the reference's way.
+// Returns false when ts is more than 2^-6 from theta (a turn no step of the tested scenarios makes): the caller then
+// runs golden_trig.
+struct SymBand { double sa, sb; }; // tie band of pass k: |e| <= sa * kGoldenInvQ[k] + sb
+
+__device__ __forceinline__ bool sym_in_band(double e, const SymBand &bd, int k)
+{
+    const double thr = fma(bd.sa, kGoldenInvQ[k], bd.sb);
+    return (__double2hiint(e) & 0x7fffffff) <= __double2hiint(thr);
+}
+
+// The whole search, the reference's way, for the rare step that has a pass inside the band: the bracket with the
+// reference's un-fused expressions (RT:184-194), the decisions from the same midpoint rule as the fast loop -- or,
+// inside the band, from the costs of both probes in the reference's expression order with libdevice's sincos.
+// Returns the final e = (a+b)/2 - ts in the fast loop's convention (sum of the midpoint moves).
+static __device__ __noinline__ double golden_sym_slow(const TieIso t, double theta, double delta, const SymBand bd)
+{
+    const CostIso cf = t.make();
+    double a = __dsub_rn(theta, RTB_DELTA_G), b = __dadd_rn(theta, RTB_DELTA_G);
+    double c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    double d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    double e = -delta;
+    for (int j = 0; j < RTB_GOLDEN_ITERS; ++j) {
+        bool left = e > 0.0;
+        if (sym_in_band(e, bd, j)) left = cf(c) < cf(d); // RT:189
+        if (left) b = d; else a = c;
+        c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+        d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+        const double q = kGoldenMid[j];
+        e += left ? -q : q;
+    }
+    return e;
+}
+
+__device__ __forceinline__ bool golden_iso_sym(double n1, double ax, double ay, const TieIso &ref, double theta,
                                                double st, double ct, double &th_out, double &s_out, double &c_out)
 {
     const double A2 = fma(ax, ax, ay * ay);
@@ -159,30 +230,25 @@ __device__ __forceinline__ bool golden_iso_sym(double n1, double ax, double ay, 
     double p = fma(t2, 1.0 / 9.0, -1.0 / 7.0);   // atan t = t - t^3/3 + t^5/5 - t^7/7 + t^9/9, |t| < 2^-6
     p = fma(p, t2, 0.2);
     p = fma(p, t2, -1.0 / 3.0);
-    const double delta = fma(t * t2, p, t), delta2 = 2.0 * delta;
+    const double delta = fma(t * t2, p, t);
     const double D = fma(-A2, rA, n1);
-    const double K = RTB_TIE_EPS * RTB_TIE_EPS;
-    const double alpha = K * (D * rA) * (D * rA), beta = K * n1 * rA;
-    double a = theta - RTB_DELTA_G, b = theta + RTB_DELTA_G;
-    double c = b - (b - a) * RTB_GOLD_RATIO;
-    double d = a + (b - a) * RTB_GOLD_RATIO;
-    int k = 0;
-#pragma unroll 1
-    while (fabs(c - d) > RTB_GOLD_TOL) {
-        const double M = ((c - theta) + (d - theta)) - delta2; // 2 (midpoint - ts)
-        bool left = M > 0.0;                                   // RT:189: if func(c) < func(d): b = d  else: a = c
-        if (M * M <= fma(alpha, kGoldenInvQ2[min(k, RTB_GOLDEN_ROT_N - 1)], beta)) left = exact_less(c, d);
-        b = left ? d : b;
-        a = left ? a : c;
-        c = b - (b - a) * RTB_GOLD_RATIO;
-        d = a + (b - a) * RTB_GOLD_RATIO;
-        ++k;
+    SymBand bd;
+    bd.sa = fabs((0.5 * RTB_TIE_EPS) * D * rA);
+    // sqrt(n1 / |A|) <= (1 + n1 / |A|) / 2; the floor covers the rounding drift of the reference's own a, b
+    bd.sb = fma(0.25 * RTB_TIE_EPS, fma(n1, rA, 1.0), RTB_TIE_FLOOR);
+    double e = -delta;                           // midpoint of [theta - pi/2, theta + pi/2] minus ts
+    bool tie = false;
+#pragma unroll
+    for (int k = 0; k < RTB_GOLDEN_ITERS; ++k) { // straight-line: 37 x (band test on the high words, sign transfer, DADD)
+        tie |= sym_in_band(e, bd, k);
+        const double q = kGoldenMid[k];          // RT:189: f(c) < f(d), i.e. e > 0: b = d, the midpoint moves left
+        e -= __hiloint2double(__double2hiint(q) | (__double2hiint(e) & 0x80000000), __double2loint(q));
     }
-    const double th = (b + a) / 2.0;
-    const double e = (th - theta) - delta, e2h = 0.5 * e * e; // |e| <= final bracket ~3e-8
+    if (tie) e = golden_sym_slow(ref, theta, delta, bd); // about one step in a thousand: redone the reference's way
+    th_out = theta + (delta + e);
+    const double e2h = 0.5 * e * e;              // |e| <= half the final bracket ~3e-8
     s_out = fma(-ss, e2h, fma(cs, e, ss));
     c_out = fma(-cs, e2h, fma(-ss, e, cs));
-    th_out = th;
     return true;
 }
 
@@ -329,36 +395,26 @@ __device__ __forceinline__ double step_fast(const DevField &f, const DevField *f
         cf.n1 = fn;
         cf.ax = fma(0.5 * h, s.gx + fgx, s.n * s.ux);
         cf.ay = fma(0.5 * h, s.gy + fgy, s.n * s.uy);
-        auto exact_less = [&](double pc, double pd) { // near-ties: both probes re-evaluated with a full sincos
-            double s1, c1, s2, c2;
-            sincos_cw_inline(pc, s1, c1);
-            sincos_cw_inline(pd, s2, c2);
-            return cf(s1, c1) < cf(s2, c2);
-        };
+        const TieIso ref = {s.n, s.ux, s.uy, s.gx, s.gy, fn, fgx, fgy, h}; // near-ties: the reference's own expression
         double ns, nc, th;
 #ifndef RTB_NO_GOLDEN_SYM
-        if (!golden_iso_sym(fn, cf.ax, cf.ay, exact_less, s.ang, s.uy, s.ux, th, ns, nc))
+        if (!golden_iso_sym(fn, cf.ax, cf.ay, ref, s.ang, s.uy, s.ux, th, ns, nc))
 #endif
-            th = golden_trig(cf, exact_less, fn, s.ang, s.uy, s.ux, ns, nc);
+            th = golden_trig(cf, ref, fn, s.ang, s.uy, s.ux, ns, nc);
         s.ang = th;
         if ((i & RTB_RESYNC_MASK) == 0) sincos_cw(s.ang, ns, nc); // periodic exact resync of the carried (sin, cos)
         s.uy = ns; s.ux = nc;
     } else { // golden, anisotropic cost RT:728,761
         CostAnisoFast cf;
-        cf.n1 = fn; cf.gamma = gamma; cf.g2m1 = g2m1;
+        cf.n1 = fn; cf.n1g2 = fn * (g2m1 + 1.0); cf.g2m1 = g2m1;
         const double ic2 = rcp_fast(s.coef * s.coef);
         const double nc = s.n * s.coef;
         cf.mx = fma(0.5 * h * s.coef, s.gx, nc * s.ux * fma(-(s.uy * s.uy), g2m1 * ic2, 1.0));
         cf.my = fma(0.5 * h * s.coef, s.gy, nc * s.uy * fma(s.ux * s.ux, g2m1 * ic2, 1.0));
         cf.gx1h = 0.5 * h * fgx; cf.gy1h = 0.5 * h * fgy;
-        auto exact_less = [&](double pc, double pd) { // near-ties: both probes re-evaluated with a full sincos
-            double s1, c1, s2, c2;
-            sincos_cw_inline(pc, s1, c1);
-            sincos_cw_inline(pd, s2, c2);
-            return cf(s1, c1) < cf(s2, c2);
-        };
+        const TieAniso ref = {s.n, s.coef, s.ux, s.uy, s.gx, s.gy, fn, fgx, fgy, h, gamma, g2m1}; // near-ties
         double nsin, ncos;
-        s.ang = golden_trig(cf, exact_less, fn * fmax(gamma, 1.0), s.ang, s.uy, s.ux, nsin, ncos);
+        s.ang = golden_trig(cf, ref, fn * fmax(gamma, 1.0), s.ang, s.uy, s.ux, nsin, ncos);
         if ((i & RTB_RESYNC_MASK) == 0) sincos_cw(s.ang, nsin, ncos);
         s.uy = nsin; s.ux = ncos;
     }

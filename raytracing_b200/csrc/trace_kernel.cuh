@@ -26,6 +26,9 @@ namespace rtb {
 #ifndef RTB_QUEUE_MIN_BLOCKS
 #define RTB_QUEUE_MIN_BLOCKS 5
 #endif
+#ifndef RTB_TRAJ_MIN_BLOCKS
+#define RTB_TRAJ_MIN_BLOCKS 5 // trajectory kernels
+#endif
 #ifndef RTB_BLOCK
 #define RTB_BLOCK 128
 #endif
@@ -313,7 +316,8 @@ __device__ __forceinline__ void ray_finish(const TraceArgs &a, int64_t r, double
 // recurrence): the parity anchor.  !EXACT = default B200 form (step_fast.cuh).
 // TMODE: 0 = no trajectory, 1 = trajectory by per-lane stores, 2 = trajectory staged in shared memory + TMA stores.
 template <int METHOD, bool ISO, int TMODE, bool EXACT, int EXTRA>
-__global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB_MIN_BLOCKS) trace_kernel(const __grid_constant__ TraceArgs a)
+__global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : TMODE ? RTB_TRAJ_MIN_BLOCKS : RTB_MIN_BLOCKS)
+trace_kernel(const __grid_constant__ TraceArgs a)
 {
     constexpr bool TRAJ = TMODE != 0;
     constexpr int UPD = updater_of(METHOD);
@@ -351,8 +355,19 @@ __global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : RTB
         const unsigned mask = __ballot_sync(0xffffffffu, alive);
         if (!mask) break;
         const bool stepped = alive;
-        if (alive) alive = ray_step<METHOD, ISO, TRAJ, EXACT, EXTRA, LAZY>(a, r, gamma, g2m1, q, i, mask, wbuf);
-        if (TRAJ && i == next_keep) { // warp-uniform: the whole warp writes its row (zeros from lanes that have ended)
+        if (alive) {
+            alive = ray_step<METHOD, ISO, TRAJ, EXACT, EXTRA, LAZY>(a, r, gamma, g2m1, q, i, mask, wbuf);
+            if (TMODE == 1 && i == next_keep) { // per-lane stores need no convergence: each lane writes its own row
+                tw.row(true, q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
+                next_keep += a.out_stride;
+            }
+        } else if (TMODE == 1) {
+            if (i == next_keep) {
+                tw.row(a.tail_zero != 0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0);
+                next_keep += a.out_stride;
+            }
+        }
+        if (TMODE == 2 && i == next_keep) { // warp-uniform: the whole warp stages its row (zeros from lanes that have ended)
             if (mask == 0xffffffffu) {
                 tw.row(true, q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
             } else {
@@ -401,42 +416,46 @@ __global__ void __launch_bounds__(RTB_BLOCK, RTB_QUEUE_MIN_BLOCKS) trace_queue_k
     int i = 0;                 // its next step index
     bool alive = false;
     bool drained = false;      // the queue is empty (warp-uniform)
-    int wait = RTB_QUEUE_WAIT; // the first iteration fills the warp
     unsigned long long steps_done = 0;
     for (;;) {
+        // compaction: finished rays leave their lanes, dead lanes take the next rays of the queue
         unsigned mask = __ballot_sync(FULL, alive);
-        if (mask != FULL && (mask == 0u || ++wait >= RTB_QUEUE_WAIT)) {
-            wait = 0;
-            if (!alive && r >= 0) { // a finished ray leaves its lane
-                ray_finish<ISO, false, false, EXTRA, LAZY>(a, r, g2m1, q);
-                steps_done += (unsigned)q.last_i;
-                r = -1;
-            }
-            if (!drained) {
-                const unsigned dead = ~mask;
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(a.queue_head, (unsigned long long)__popc(dead));
-                base = __shfl_sync(FULL, base, 0);
-                drained = base >= (unsigned long long)a.R;
-                if (!drained && !alive) {
-                    const int64_t nr = (int64_t)base + __popc(dead & ((1u << lane) - 1u));
-                    if (nr < a.R) {
-                        r = nr;
-                        ray_init<METHOD, ISO, false, false, EXTRA>(a, r, gamma, g2m1, q);
-                        i = q.i_start;
-                        alive = i < q.M; // a ray without steps (max_size 1) is finished at the next compaction
-                    }
-                }
-                mask = __ballot_sync(FULL, alive);
-            }
-            if (mask == 0u) {
-                if (drained && !__any_sync(FULL, r >= 0)) break;
-                continue;
-            }
+        if (!alive && r >= 0) {
+            ray_finish<ISO, false, false, EXTRA, LAZY>(a, r, g2m1, q);
+            steps_done += (unsigned)q.last_i;
+            r = -1;
         }
-        if (alive) {
-            alive = ray_step<METHOD, ISO, false, false, EXTRA, LAZY>(a, r, gamma, g2m1, q, i, mask, wbuf);
-            ++i;
+        if (!drained) {
+            const unsigned dead = ~mask;
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(a.queue_head, (unsigned long long)__popc(dead));
+            base = __shfl_sync(FULL, base, 0);
+            drained = base >= (unsigned long long)a.R;
+            if (!drained && !alive) {
+                const int64_t nr = (int64_t)base + __popc(dead & ((1u << lane) - 1u));
+                if (nr < a.R) {
+                    r = nr;
+                    ray_init<METHOD, ISO, false, false, EXTRA>(a, r, gamma, g2m1, q);
+                    i = q.i_start;
+                    alive = i < q.M; // a ray without steps (max_size 1) is finished at the next compaction
+                }
+            }
+            mask = __ballot_sync(FULL, alive);
+        }
+        if (mask == 0u) {
+            if (drained && !__any_sync(FULL, r >= 0)) break;
+            continue;
+        }
+        // the step loop, same shape as trace_kernel's; left when the warp has been running with dead lanes for
+        // RTB_QUEUE_WAIT iterations (or has none alive)
+        int wait = 0;
+        for (;;) {
+            mask = __ballot_sync(FULL, alive);
+            if (mask != FULL && (mask == 0u || ++wait > RTB_QUEUE_WAIT)) break;
+            if (alive) {
+                alive = ray_step<METHOD, ISO, false, false, EXTRA, LAZY>(a, r, gamma, g2m1, q, i, mask, wbuf);
+                ++i;
+            }
         }
     }
     if (a.total_steps) { // one atomic per warp

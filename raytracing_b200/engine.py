@@ -264,7 +264,7 @@ class Engine:
 
     def trace(self, method, theta0, x0, y0, step, max_size, gamma, box, interface=False, full=True,
               out_stride=1, want_last_row=True, want_px_stats=False, want_errors=None, exact=False,
-              steps=None, max_sizes=None, out=None, tail_zero=True, static_grid=False):
+              steps=None, max_sizes=None, out=None, tail_zero=True, static_grid=False, ray_queue=False):
         """trazar's integration for an explicit fan.
 
         Inputs are numpy arrays (host pointers, staged inside the call) or torch CUDA tensors
@@ -302,7 +302,7 @@ class Engine:
         last_row = out.get("last_row", empty(6, R) if want_last_row else None)
         px_stats = out.get("px_stats", empty(3, R) if want_px_stats else None)
         flags = (_cabi.RTB_F_INTERFACE if interface else 0) | (_cabi.RTB_F_EXACT_BASIS if exact else 0) | \
-                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO) | (_cabi.RTB_F_STATIC_GRID if static_grid else 0)
+                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO) | (_cabi.RTB_F_STATIC_GRID if static_grid else 0) | (_cabi.RTB_F_RAY_QUEUE if ray_queue else 0)
         steps_a = max_sizes_a = None
         if steps is not None:
             if dev:

@@ -40,8 +40,11 @@ def assert_close(a, b, tol, what=""):
     ok = close(a, b, tol)
     if not ok.all():
         a, b = np.asarray(a), np.asarray(b)
-        bad = np.abs(a - b)[~ok].max()
-        raise AssertionError("%s: max |delta| %.3e exceeds tol %.1e (%d of %d entries)" % (what, bad, tol, (~ok).sum(), ok.size))
+        a, b = np.broadcast_arrays(a, b)
+        err = np.where(ok, 0.0, np.abs(a - b))
+        at = np.unravel_index(np.argmax(err), err.shape)
+        raise AssertionError("%s: max |delta| %.3e exceeds tol %.1e (%d of %d entries); worst at index %s: got %.17g, want %.17g"
+                             % (what, err.max(), tol, (~ok).sum(), ok.size, at, a[at], b[at]))
 
 
 def check_steps(got, ref, tol, what=""):

@@ -23,6 +23,29 @@ def _oracle_final(s, uc, m, th, x0, y0):
     return O.trace(m, s["z"], s["grd"], s["step"], s["M"], s["gamma"], s["box"], False, th, x0, y0, full=False, nthreads=16)
 
 
+def _measured_tolerance(s, uc, m, th, x0, y0, base, tol):
+    """tests/_util.py's policy applied to THESE rays: how far the reference algorithm's own outputs move when every
+    sin/cos result is replaced by a neighbouring double (oracle noise probe).  Needed where the reference is
+    ill-conditioned and the dense fans reach places the 31-ray default fans of sensitivity.json do not: curvature_t
+    divides a cancelling difference by a curvature just above GOLD_TOL (RT:361-363) for rays ever closer to the
+    vertical, finite_diff amplifies noise.  Returns (tolerance dict, rays whose step count the noise itself moves)."""
+    from oracle import rt_oracle as O
+    from _util import SAFETY
+    dev_all = dev_d = 0.0
+    unstable = np.zeros(th.size, dtype=bool)
+    try:
+        for seed in (1, 2, 3):
+            O.set_trig_noise(seed)
+            r = _oracle_final(s, uc, m, th, x0, y0)
+            same = base["d_ray"][2] == r["d_ray"][2]
+            unstable |= ~same
+            dev_all = max(dev_all, float(np.abs(base["final"] - r["final"])[:, same].max()))
+            dev_d = max(dev_d, float(np.abs(base["d_ray"][:2] - r["d_ray"][:2])[:, same].max()))
+    finally:
+        O.set_trig_noise(0)
+    return dict(tol, all=max(tol["all"], SAFETY * dev_all), d_ray=max(tol["d_ray"], SAFETY * dev_d)), unstable
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # Dense fans: the WHOLE fan is launched (>= 2^20 rays: warp-staged cell records, 128-thread blocks, ray queue), sampled
 # rays are compared with the oracle and with the rows the unmodified reference produced for rays of these very fans
@@ -55,7 +78,7 @@ def test_dense_fan_vs_oracle_and_reference(engine, golden_traj, sensitivity, uc,
     rng = np.random.default_rng(100 * int(uc) + m)
     for lo in starts:
         th, x0, y0 = rt.make_fan(uc, R, lo, lo + n)
-        r = engine.trace(m, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], full=False)
+        r = engine.trace(m, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], full=False)   # static grid
         d = r.d_ray.cpu().numpy()
         last = r.last_row.cpu().numpy()
         assert r.stats["ray_steps"] == int(d[2].sum()) and r.stats["nonfinite_rays"] == 0
@@ -66,7 +89,13 @@ def test_dense_fan_vs_oracle_and_reference(engine, golden_traj, sensitivity, uc,
                                          [i - lo for i in gidx if lo <= i < lo + n]])).astype(int)
         o = _oracle_final(s, uc, m, th[pick], x0[pick], y0[pick])
         what = "dense s%s op%d slice %d" % (uc, m, lo)
+        if m in (3, 4, 5, 7, 10):
+            tol_m, unstable = _measured_tolerance(s, uc, m, th[pick], x0[pick], y0[pick], o, tol)
+            assert unstable.mean() < 0.1 and np.abs(d[2, pick] - o["d_ray"][2])[unstable].max(initial=0) <= 1
+            pick, o = pick[~unstable], {k: (v[..., ~unstable] if isinstance(v, np.ndarray) else v) for k, v in o.items()}
+            tol = dict(tol, all=tol_m["all"], d_ray=tol_m["d_ray"])
         same = check_steps(d[2, pick], o["d_ray"][2], tol, what)
+        what += " rays %s..%s" % (lo + pick[0], lo + pick[-1])
         assert_close(last[:, pick][:, same], o["final"][:, same], tol["all"], what + " last_row")
         assert_close(d[:2, pick][:, same], o["d_ray"][:2, same], tol["d_ray"], what + " d_ray")
         # (b) the reference's own rows for the fixture rays
@@ -78,9 +107,9 @@ def test_dense_fan_vs_oracle_and_reference(engine, golden_traj, sensitivity, uc,
                 if ok.all():
                     assert_close(last[:, k], golden_traj[key + "last_row"][:, j], tol["all"], what + " golden last_row")
                     assert_close(d[:2, k], gd[:2], tol["d_ray"], what + " golden d_ray")
-        # (c) the static grid (one thread per ray) gives the same bits as the ray queue
+        # (c) the ray queue (persistent warps, compaction) gives the same bits as the static grid
         if m in (6, 1, 11):
-            st = engine.trace(m, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], full=False, static_grid=True)
+            st = engine.trace(m, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], full=False, ray_queue=True)
             assert torch.equal(st.d_ray, r.d_ray) and torch.equal(st.last_row, r.last_row)
 
 
@@ -92,7 +121,7 @@ def test_interface_dense_fan_vs_oracle(engine, sensitivity):
     tol = tolerances(sensitivity, "1", 6)
     R = 1 << 18
     th, x0, y0 = rt.make_fan("1", R)
-    r = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], interface=True, full=False)
+    r = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], interface=True, full=False, ray_queue=True)
     pick = np.unique(np.concatenate([np.arange(7000, 7040), np.linspace(0, R - 1, 24).astype(int)]))
     o = O.trace(6, s["z"], s["grd"], s["step"], s["M"], s["gamma"], s["box"], True, th[pick], x0[pick], y0[pick], full=True,
                 nthreads=16)
@@ -126,7 +155,8 @@ def test_ray_queue_equals_static_grid(engine, case):
         M = int(msz.max())
     if case == "aniso_stats":
         M = 1200
-    a = engine.trace(m, *_dev(th, x0, y0), None if case == "mixed_steps" else s["step"], M, s["gamma"], s["box"], **kw)
+    a = engine.trace(m, *_dev(th, x0, y0), None if case == "mixed_steps" else s["step"], M, s["gamma"], s["box"],
+                     ray_queue=True, **kw)
     b = engine.trace(m, *_dev(th, x0, y0), None if case == "mixed_steps" else s["step"], M, s["gamma"], s["box"],
                      static_grid=True, **kw)
     for name in ("d_ray", "last_row", "px_stats") + (("errors",) if uc == "1" else ()):

@@ -10,6 +10,7 @@ FL="-O3 -std=c++17 -lineinfo $ARCH -Xcompiler -fPIC -Xptxas -v $@"
 pids=()
 ( nvcc $FL -c $src/rtb.cu -o $out/rtb.o 2> $out/rtb.log ) & pids+=($!)
 ( nvcc $FL -c $src/shoot.cu -o $out/shoot.o 2> $out/shoot.log ) & pids+=($!)
+( nvcc $FL -c $src/sweep.cu -o $out/sweep.o 2> $out/sweep.log ) & pids+=($!)
 ( nvcc $FL -c $src/wavefront.cu -o $out/wavefront.o 2> $out/wavefront.log ) & pids+=($!)
 ( nvcc $FL -c $src/fit.cu -o $out/fit.o 2> $out/fit.log ) & pids+=($!)
 for m in 1 2 3 4 5 6 7 8 9 10 11; do
@@ -17,4 +18,4 @@ for m in 1 2 3 4 5 6 7 8 9 10 11; do
 done
 for p in ${pids[@]}; do wait $p; done
 nvcc -shared $ARCH -o $out/librtb.so $out/*.o
-grep -A2 "trace_kernelILi6ELb1ELb0ELb0ELb0EEE" $out/trace_m6.log | grep -E "spill|Used" | head -2
+grep -A2 "trace_kernelILi6ELb1ELi[012]ELb0ELi0E\|trace_queue_kernelILi6ELb1ELi0E" $out/trace_m6.log | grep -E "Compiling|spill|Used"
