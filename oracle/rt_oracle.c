@@ -43,8 +43,12 @@ static inline double noisy(double r)
     if (b == 1) return nextafter(r, -INFINITY);
     return r;
 }
-static inline double rsin(double x) { return noisy(sin(x)); }
-static inline double rcos(double x) { return noisy(cos(x)); }
+/* Seeds >= 1000 additionally move the ARGUMENT of every sin/cos by +-1 ulp: the angle another correct implementation
+ * carries differs from the reference's by the rounding of its own additions, and where the reference evaluates
+ * sin(theta + d) - sin(theta) for a tiny d (curvature_t, RT:361-363) the rounding of theta + d alone moves the step
+ * by ulp(theta)/curvature -- noise the result-only probe cannot see because oracle and reference round alike. */
+static inline double rsin(double x) { return noisy(sin(g_noise >= 1000 ? noisy(x) : x)); }
+static inline double rcos(double x) { return noisy(cos(g_noise >= 1000 ? noisy(x) : x)); }
 
 typedef struct {
     const double *tu; /* knots of the first spline axis (physical y, RT:455-457) */

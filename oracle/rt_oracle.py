@@ -120,7 +120,7 @@ def max_threads():
 
 def set_trig_noise(seed):
     """0 = off (faithful oracle); >0 = every sin/cos result moved by +-1 ulp with probability 1/2
-    (sensitivity probe of the reference algorithm, see rt_oracle.c)."""
+    (sensitivity probe of the reference algorithm, see rt_oracle.c); >= 1000 = the arguments of sin/cos as well."""
     lib().rto_set_trig_noise(int(seed))
 
 

@@ -78,27 +78,15 @@ struct CostAnisoFast {
 //
 // Near-ties are where the rounding of *any* evaluation decides (among them the exact tie of a ray running along
 // grad n): |f(c) - f(d)| within ~16 ulp-level perturbations of the residuals.  They are decided the reference's way,
-// out of line: the probes c, d of that pass are rebuilt from the decision bits with the reference's own un-fused
-// expressions (golden_probes_at), and both costs are evaluated afresh in the reference's expression order (CostIso /
-// CostAniso of step.cuh) with libdevice's sincos -- no cached value, no angle-addition chain.  About one step in a
-// thousand per warp on the benchmark fans (ncu source counters, profiles/).
+// out of line: the search so far is replayed next to the reference's own un-fused bracket arithmetic (GoldenBracket),
+// and both costs of the pass are evaluated afresh at the reference's probes c, d in the reference's expression order
+// (CostIso / CostAniso of step.cuh) with libdevice's sincos -- no cached value, no angle-addition chain.  About one
+// step in a thousand (symmetric cost) to a few in a hundred (anisotropic cost) per warp on the benchmark fans (ncu
+// source counters, profiles/).
 // ------------------------------------------------------------------------------------------------------------------
 #ifndef RTB_TIE_FLOOR
 #define RTB_TIE_FLOOR 2.0e-14 // covers the rounding drift of the reference's own a, b (37 passes x ulp(theta +- pi/2))
 #endif
-
-static __device__ __noinline__ double2 golden_probes_at(double theta, unsigned long long bits, int k)
-{
-    double a = __dsub_rn(theta, RTB_DELTA_G), b = __dadd_rn(theta, RTB_DELTA_G);
-    double c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
-    double d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
-    for (int j = 0; j < k; ++j) {
-        if ((bits >> j) & 1ull) b = d; else a = c; // RT:189-192
-        c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
-        d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
-    }
-    return make_double2(c, d);
-}
 
 // What a near-tie needs to rebuild the reference's cost lambda: the step's inputs as they sit in registers anyway
 // (nothing is computed for it unless a tie occurs).
@@ -127,53 +115,124 @@ struct TieAniso { // RT:725-729, 758-762
     }
 };
 
-template <class TIE>
-static __device__ __noinline__ bool golden_tie(const TIE t, double theta, unsigned long long bits, int k)
+// The reference's bracket (RT:184-194), un-fused.
+struct GoldenBracket {
+    double a, b, c, d;
+    __device__ __forceinline__ void probes()
+    {
+        c = __dsub_rn(b, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+        d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
+    }
+    __device__ __forceinline__ void init(double theta)
+    {
+        a = __dsub_rn(theta, RTB_DELTA_G); b = __dadd_rn(theta, RTB_DELTA_G);
+        probes();
+    }
+    __device__ __forceinline__ void shrink(bool left) // RT:189-194
+    {
+        if (left) b = d; else a = c;
+        probes();
+    }
+};
+
+// Evaluating search (anisotropic cost; isotropic cost when the turn is too large for golden_iso_sym).  State of a pass:
+// the kept probe W and the newest probe N (sin, cos, cost), on which side N lies, and the bracket midpoint - theta.
+struct TrigState {
+    double Ws, Wc, Wf, Ns, Nc, Nf, m;
+    bool nl; // N is the left probe (c)
+};
+
+template <class F>
+__device__ __forceinline__ void trig_init(const F &cost, double st, double ct, TrigState &g)
 {
-    const double2 p = golden_probes_at(theta, bits, k);
-    const auto cf = t.make();
-    return cf(p.x) < cf(p.y); // RT:189
+    const double S0 = kGolden0[0], C0 = kGolden0[1];
+    // the first probes: c = theta - P0 (left, kept), d = theta + P0 (right, newest)
+    g.Ws = fma(-ct, S0, st * C0); g.Wc = fma(st, S0, ct * C0);
+    g.Ns = fma(ct, S0, st * C0); g.Nc = fma(-st, S0, ct * C0);
+    g.Wf = cost(g.Ws, g.Wc); g.Nf = cost(g.Ns, g.Nc);
+    g.nl = false;
+    g.m = 0.0;
 }
 
-// Evaluating search (anisotropic cost; isotropic cost when the turn is too large for golden_iso_sym).  `cost(s, c)` is
-// the fast form of the cost, `ref` the reference-order functor used for near-ties, `scale` the size of the terms the
-// residual is the difference of.  The probe created in pass k sits at the kept probe -+ pi rho^(k+4) (kGoldenRot):
-// one rotation by table constants and one cost evaluation per pass; the kept probe keeps its cost.
-// Returns theta_new and its sin/cos.
-template <class F, class REF>
-__device__ __forceinline__ double golden_trig(const F &cost, const REF &ref, double scale, double theta, double st,
+// f(c) - f(d) inside the rounding noise of the residuals?  df^2 <= tie2 * (f(c) + f(d)), compared on the high words
+// (a superset of the exact comparison; f(c) + f(d) >= max f).
+__device__ __forceinline__ bool trig_in_band(const TrigState &g, double tie2, double &df)
+{
+    df = g.Nf - g.Wf;
+    return __double2hiint(df * df) <= __double2hiint(tie2 * (g.Nf + g.Wf));
+}
+
+// RT:189 `if func(c) < func(d)` from the sign of f(N) - f(W): c is N when nl
+__device__ __forceinline__ bool trig_decide(const TrigState &g, double df) { return (__double2hiint(df) < 0) == g.nl; }
+
+// After the decision of pass k: the kept probe (c when b moves, d when a moves), the midpoint move, and the new probe
+// at the kept one -+ pi rho^(k+4): one rotation by table constants, one cost evaluation.  Signs by integer transfer.
+template <class F>
+__device__ __forceinline__ void trig_advance(const F &cost, TrigState &g, bool left, int k)
+{
+    if (left == g.nl) { g.Ws = g.Ns; g.Wc = g.Nc; g.Wf = g.Nf; }
+    const int sgn = left ? (int)0x80000000 : 0;
+    const double q = kGoldenMid[k];
+    g.m += __hiloint2double(__double2hiint(q) ^ sgn, __double2loint(q)); // left: the midpoint moves by -q
+    const double2 r = kGoldenRot[k];
+    const double sr = __hiloint2double(__double2hiint(r.x) ^ sgn, __double2loint(r.x)); // the new probe lies left of the kept one when b moved
+    g.Ns = fma(g.Wc, sr, g.Ws * r.y);
+    g.Nc = fma(-g.Ws, sr, g.Wc * r.y);
+    g.Nf = cost(g.Ns, g.Nc);
+    g.nl = left;
+}
+
+// Decision of pass k the reference's way, for a pass whose costs are inside the band.  Nothing about the earlier
+// passes is kept by the fast loop, so they are replayed here -- same fast arithmetic, same decisions -- next to the
+// reference's own bracket; a pass inside the band (this one, and any earlier one) is decided by the costs of the
+// reference's probes c, d in the reference's expression order with libdevice's sincos.
+template <class F, class TIE>
+static __device__ __noinline__ bool golden_trig_tie(const F cost, const TIE t, double tie2, double theta, double st, double ct, int k)
+{
+    const auto cf = t.make();
+    GoldenBracket br;
+    br.init(theta);
+    TrigState g;
+    trig_init(cost, st, ct, g);
+    for (int j = 0;; ++j) {
+        double df;
+        bool left;
+        if (trig_in_band(g, tie2, df)) left = cf(br.c) < cf(br.d); // RT:189
+        else left = trig_decide(g, df);
+        if (j == k) return left;
+        br.shrink(left);
+        trig_advance(cost, g, left, j);
+    }
+}
+
+template <class F, class TIE>
+__device__ __forceinline__ double golden_trig(const F &cost, const TIE &ref, double scale, double theta, double st,
                                               double ct, double &s_out, double &c_out)
 {
     const double tie2 = (RTB_TIE_EPS * scale) * (RTB_TIE_EPS * scale);
-    const double S0 = kGolden0[0], C0 = kGolden0[1];
-    // the first probes: c = theta - P0 (left), d = theta + P0 (right)
-    double Ws = fma(-ct, S0, st * C0), Wc = fma(st, S0, ct * C0);   // kept probe W := c
-    double Ns = fma(ct, S0, st * C0), Nc = fma(-st, S0, ct * C0);   // newest probe N := d
-    double Wf = cost(Ws, Wc), Nf = cost(Ns, Nc);
-    bool nl = false;          // N is the left probe (c)
-    double m = 0.0;           // bracket midpoint - theta
-    unsigned long long bits = 0;
+    TrigState g;
+    trig_init(cost, st, ct, g);
+    // The passes run in a call-free inner loop (its state stays in registers); a pass inside the band leaves it, is
+    // decided out of line, and the loop resumes behind it.
+    int k = 0;
+    for (;;) {
+        bool band = false;
+        double df;
 #pragma unroll 1
-    for (int k = 0; k < RTB_GOLDEN_ITERS; ++k) {
-        const double df = Nf - Wf;
-        bool left = nl ? (df < 0.0) : (df > 0.0); // RT:189: if func(c) < func(d): b = d  else: a = c
-        if (df * df <= tie2 * fmax(Nf, Wf)) left = golden_tie(ref, theta, bits, k);
-        bits |= (unsigned long long)left << k;
-        if (left == nl) { Ws = Ns; Wc = Nc; Wf = Nf; } // the kept probe: c when b moves, d when a moves
-        const double q = kGoldenMid[k];
-        m += left ? -q : q;
-        const double2 r = kGoldenRot[k];
-        const double sr = left ? -r.x : r.x;      // the new probe lies left of the kept one when b moved
-        Ns = fma(Wc, sr, Ws * r.y);
-        Nc = fma(-Ws, sr, Wc * r.y);
-        Nf = cost(Ns, Nc);
-        nl = left;
+        for (; k < RTB_GOLDEN_ITERS; ++k) {
+            if (trig_in_band(g, tie2, df)) { band = true; break; }
+            trig_advance(cost, g, trig_decide(g, df), k);
+        }
+        if (!band) break;
+        const bool left = golden_trig_tie(cost, ref, tie2, theta, st, ct, k);
+        trig_advance(cost, g, left, k);
+        ++k;
     }
     // (a+b)/2 lies half a probe distance from the kept probe: to its left when the kept probe is d (N is c)
-    const double e = nl ? -RTB_GOLDEN_FINAL_HALF : RTB_GOLDEN_FINAL_HALF, e2h = 0.5 * e * e;
-    s_out = fma(-Ws, e2h, fma(Wc, e, Ws));
-    c_out = fma(-Wc, e2h, fma(-Ws, e, Wc));
-    return theta + m;
+    const double e = g.nl ? -RTB_GOLDEN_FINAL_HALF : RTB_GOLDEN_FINAL_HALF, e2h = 0.5 * e * e;
+    s_out = fma(-g.Ws, e2h, fma(g.Wc, e, g.Ws));
+    c_out = fma(-g.Wc, e2h, fma(-g.Ws, e, g.Wc));
+    return theta + g.m;
 }
 
 // Isotropic cost without evaluating it: f(t) = |n1 (cos t, sin t) - A|^2 = n1^2 + |A|^2 - 2 n1 |A| cos(t - ts) is

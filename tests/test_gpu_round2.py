@@ -34,7 +34,7 @@ def _measured_tolerance(s, uc, m, th, x0, y0, base, tol):
     dev_all = dev_d = 0.0
     unstable = np.zeros(th.size, dtype=bool)
     try:
-        for seed in (1, 2, 3):
+        for seed in (1, 2, 3, 1001, 1002, 1003):     # results of sin/cos +-1 ulp; from 1000 on their arguments too
             O.set_trig_noise(seed)
             r = _oracle_final(s, uc, m, th, x0, y0)
             same = base["d_ray"][2] == r["d_ray"][2]
