@@ -69,9 +69,9 @@ typedef struct {
 
 #define RTB_F_STATIC_GRID 8u  /* one thread per ray for the whole launch (the only mapping for trajectories) */
 #define RTB_F_RAY_QUEUE 16u   /* FINAL-type outputs of fans >= 2^16 rays: persistent warps pull rays from a queue and
-                                 compact when lanes finish (warp ballot + refill of the dead lanes) -- for fans whose
-                                 neighbouring rays differ widely in length (unsorted launch angles).  Chosen
-                                 automatically for launches with per-ray max_sizes; results are bit-identical either way */
+                                 compact when lanes finish (warp ballot + refill of the dead lanes).  Opt-in: meant for
+                                 fans whose neighbouring rays differ widely in length, but on every fan measured on B200
+                                 the static grid is as fast or faster; results are bit-identical either way */
 
 typedef struct {
     int32_t method;     /* 1..11 = op1..op11 (RT:469-764); the shim maps function objects to ids  */
@@ -112,7 +112,7 @@ int rtb_abi_version(void);
 /* Hex digest of the CUDA sources the library was compiled from (written by csrc/Makefile): lets a caller check that a
    prebuilt librtb.so matches the source tree it sits in. */
 const char *rtb_build_id(void);
-/* Tuning / test switches of a context.  RTB_OPT_QUEUE: 0 = auto (ray queue for large launches with per-ray max_sizes),
+/* Tuning / test switches of a context.  RTB_OPT_QUEUE: 0 = per call (RTB_F_RAY_QUEUE / RTB_F_STATIC_GRID; default static),
    1 = always where possible, 2 = never (static grid).  RTB_OPT_TRAJ_STORE: 0 = auto (trajectory rows leave through
    shared memory as 256-byte bulk copies when R is even), 1 = per-lane st.global. */
 #define RTB_OPT_QUEUE 1

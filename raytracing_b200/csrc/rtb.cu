@@ -305,13 +305,12 @@ int rtb_launch(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, TraceArgs a, 
     c.block = a.lane_shift ? 32 : ctx->block;
     // Ray queue + warp compaction: FINAL-type outputs of the default kernels on fans of at least a wave; the static
     // grid keeps trajectories (coalesced rows need thread <-> ray fixed), the faithful kernels and spread small fans.
-    // Chosen by default (RTB_OPT_QUEUE 0) where rays of one warp can differ widely in length -- launches with per-ray
-    // max_sizes (mixed DELTA_S candidates, converged and unconverged shooting pairs); angle-sorted fans of one step
-    // size end warp by warp and run 8-10 % faster on the static grid (profiles/r2b_time_r2.txt), RTB_OPT_QUEUE 1 or the
-    // caller's knowledge of an unsorted fan (RTB_F_RAY_QUEUE) overrides.
+    // Opt-in (RTB_F_RAY_QUEUE per call, RTB_OPT_QUEUE 1 per context): on every fan measured so far -- angle-sorted,
+    // shuffled, DELTA_S candidates mixed inside warps -- the static grid is 1-12 % faster (profiles/r2c_time_r2.txt):
+    // rays that diverge in length also diverge in position, and then the step is bound by the 32 different cell records
+    // a warp has to fetch, not by idle lanes; the hardware block scheduler already refills SMs block by block.
     const bool can_queue = !traj && !c.exact && a.lane_shift == 0 && a.stage && (p->flags & RTB_F_STATIC_GRID) == 0;
-    c.queue = can_queue && (ctx->queue_mode == 1 || (p->flags & RTB_F_RAY_QUEUE) != 0 ||
-                            (ctx->queue_mode == 0 && a.max_sizes != nullptr && a.cand_R == 0));
+    c.queue = can_queue && (ctx->queue_mode == 1 || (p->flags & RTB_F_RAY_QUEUE) != 0);
     c.queue_blocks = ctx->sm_count * RTB_QUEUE_MIN_BLOCKS;
     if (c.queue) {
         const int64_t need = (a.R + RTB_BLOCK - 1) / RTB_BLOCK;

@@ -346,6 +346,7 @@ trace_kernel(const __grid_constant__ TraceArgs a)
     int next_keep = a.out_stride; // next step index whose row is kept in s_ray
 
     bool alive = valid && q.i_start < q.M;
+    if (TMODE == 2 && !alive) tw.ended(); // a ray without steps, or a lane past the end of the fan
     int i = q.i_start;
     // The loop condition must be warp-uniform (lanes may have different M with per-ray max_sizes):
     // every lane iterates until no lane of the warp is alive; `alive` drops at i+1 >= M.
@@ -367,15 +368,12 @@ trace_kernel(const __grid_constant__ TraceArgs a)
                 next_keep += a.out_stride;
             }
         }
-        if (TMODE == 2 && i == next_keep) { // warp-uniform: the whole warp stages its row (zeros from lanes that have ended)
-            if (mask == 0xffffffffu) {
-                tw.row(true, q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
-            } else {
-                const double z = 0.0;
-                tw.row(stepped || a.tail_zero != 0, stepped ? q.s.x : z, stepped ? q.s.y : z, stepped ? q.px : z,
-                       stepped ? q.py : z, stepped ? q.T : z, stepped ? q.s.ang : z);
+        if (TMODE == 2) {
+            if (i == next_keep) { // warp-uniform: the whole warp stages its row (lanes whose ray has ended store nothing)
+                tw.row(stepped, q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
+                next_keep += a.out_stride;
             }
-            next_keep += a.out_stride;
+            if (stepped && !alive) tw.ended(); // rows this ray will not reach read as zeros (np.zeros RT:802)
         }
     }
     if (TRAJ) { // rows after the last step of every ray of this warp

@@ -39,6 +39,7 @@ template <> struct TrajWriter<0> {
     __device__ __forceinline__ void init(double *, const TrajMaps *, int64_t, int64_t, bool, unsigned char *) {}
     __device__ __forceinline__ void row(bool, double, double, double, double, double, double) {}
     __device__ __forceinline__ void zero_tail(int, bool) {}
+    __device__ __forceinline__ void ended() {}
     __device__ __forceinline__ void finish() {}
 };
 
@@ -67,25 +68,29 @@ template <> struct TrajWriter<1> { // per-lane stores
                 gp += 6 * R;
             }
     }
+    __device__ __forceinline__ void ended() {}
     __device__ __forceinline__ void finish() {}
 };
 
 template <> struct TrajWriter<2> { // staged rows + TMA stores
     const TrajMaps *maps;
     double *buf;           // the warp's staging slice [RTB_TRAJ_ROWS][6][32]
+    double *mine;          // this lane's column of it
     int x0, y;             // first ray of the warp, (next unflushed row) * 6
     int k;                 // rows staged and not yet flushed
     int lane;
     bool any;              // the warp holds at least one ray of the fan
+    bool zero_pending;     // this lane's ray has ended: its column is cleared at the start of the next tile
 
     __device__ __forceinline__ void init(double *, const TrajMaps *maps_, int64_t R, int64_t r, bool, unsigned char *smem)
     {
-        k = 0; maps = maps_;
+        k = 0; maps = maps_; zero_pending = false;
         lane = threadIdx.x & 31;
         const int64_t r0 = r - lane;
         x0 = (int)r0; y = 0;
         any = r0 < R;
         buf = reinterpret_cast<double *>(smem) + (size_t)(threadIdx.x >> 5) * (RTB_TRAJ_ROWS * 6 * 32);
+        mine = buf + lane;
     }
 
     // the TMA stores of the previous flush have finished READING the staging slice
@@ -115,14 +120,39 @@ template <> struct TrajWriter<2> { // staged rows + TMA stores
         y += 6 * n;
     }
 
-    // One kept row; must be called by all 32 lanes of the warp together (a lane whose ray has ended passes zeros:
-    // the tile covers the whole warp, and zeros are what np.zeros left there, RT:802).
-    __device__ __forceinline__ void row(bool, double x, double yv, double px, double py, double T, double ang)
+    __device__ __forceinline__ void clear_rows(int from)
     {
-        if (k == 0) reads_done();
-        double *b = buf + k * (6 * 32) + lane;
-        b[0] = x; b[32] = yv; b[64] = px; b[96] = py; b[128] = T; b[160] = ang;
+#pragma unroll
+        for (int j = 0; j < RTB_TRAJ_ROWS; ++j)
+            if (j >= from) {
+                double *b = mine + j * (6 * 32);
+                b[0] = 0.0; b[32] = 0.0; b[64] = 0.0; b[96] = 0.0; b[128] = 0.0; b[160] = 0.0;
+            }
+    }
+
+    // One kept row; called by all 32 lanes of the warp together.  A lane whose ray has ended (live == false) stores
+    // nothing: its column of the slice was cleared when the ray ended (ended()), and zeros are what np.zeros left in
+    // the rows after a ray's last step (RT:802).
+    __device__ __forceinline__ void row(bool live, double x, double yv, double px, double py, double T, double ang)
+    {
+        if (k == 0) {
+            reads_done();
+            if (zero_pending) { clear_rows(0); zero_pending = false; }
+        }
+        if (live) {
+            double *b = mine + k * (6 * 32);
+            b[0] = x; b[32] = yv; b[64] = px; b[96] = py; b[128] = T; b[160] = ang;
+        }
         if (++k == RTB_TRAJ_ROWS) { flush(RTB_TRAJ_ROWS); k = 0; }
+    }
+
+    // This lane's ray has just stored its last row: the rows of the current tile it will not reach are cleared now
+    // (the previous flush has finished reading them: reads_done ran when this tile was begun), the rest of its column
+    // at the start of the next tile.
+    __device__ __forceinline__ void ended()
+    {
+        clear_rows(k);
+        zero_pending = true;
     }
 
     // n more rows of zeros (np.zeros RT:802) after the last step of every ray of the warp.
@@ -131,8 +161,7 @@ template <> struct TrajWriter<2> { // staged rows + TMA stores
         if (k > 0) { flush(k); k = 0; }
         if (!tail_zero || n <= 0) return;
         reads_done();
-#pragma unroll
-        for (int j = 0; j < RTB_TRAJ_ROWS * 6; ++j) buf[j * 32 + lane] = 0.0;
+        clear_rows(0);
         // the same zero tile serves every remaining flush: no shared-memory writes in between
         for (; n > 0; n -= RTB_TRAJ_ROWS) flush(min(n, RTB_TRAJ_ROWS));
     }
