@@ -394,7 +394,7 @@ def run_cuda(args):
                 best = rf
         gbs = best.stats["ray_steps"] * 48 / (best.stats["kernel_ms"] * 1e-3) / 1e9
         full_info = {"ms": best.stats["kernel_ms"], "ray_steps_per_s": best.stats["ray_steps"] / (best.stats["kernel_ms"] * 1e-3),
-                     "hbm_write_gbs": gbs, "kernel": "trace_kernel<6,iso,traj=staged rows + 2-D TMA stores>"}
+                     "hbm_write_gbs": gbs, "kernel": "trace_kernel<6,iso,traj=per-lane st.global.cs>"}
         del s_ray
         torch.cuda.empty_cache()
         trazar_full = e2e_trazar_full(rt, eng, z, grd, step)

@@ -113,10 +113,11 @@ int rtb_abi_version(void);
    prebuilt librtb.so matches the source tree it sits in. */
 const char *rtb_build_id(void);
 /* Tuning / test switches of a context.  RTB_OPT_QUEUE: 0 = per call (RTB_F_RAY_QUEUE / RTB_F_STATIC_GRID; default static),
-   1 = always where possible, 2 = never (static grid).  RTB_OPT_TRAJ_STORE: 0 = auto (trajectory rows leave through
-   shared memory as 256-byte bulk copies when R is even), 1 = per-lane st.global. */
+   1 = always where possible, 2 = never (static grid).  RTB_OPT_TRAJ_STORE: 0 = per-lane st.global.cs (default: faster
+   on B200), 1 = trajectory rows staged in shared memory, 2-D TMA stores (needs R even). */
 #define RTB_OPT_QUEUE 1
 #define RTB_OPT_TRAJ_STORE 2
+#define RTB_OPT_SHOOT_GROUPS 3 /* rtb_shoot_refine: groups of pairs iterating on their own streams, 1..16; 0 = auto */
 int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value);
 
 /*

@@ -40,10 +40,15 @@ struct rtb_ctx {
     int sm_count = 148;
     int queue_slot = 2; // d_total slot of the last ray-queue launch (round robin over RTB_COUNTER_SLOTS - 2)
     int queue_mode = 0; // rtb_set_option(RTB_OPT_QUEUE): 0 = auto, 1 = always the ray-queue kernel, 2 = never
-    int traj_mode = 0;  // rtb_set_option(RTB_OPT_TRAJ_STORE): 0 = auto (bulk copies when aligned), 1 = per-lane stores
+    int traj_mode = 0;  // rtb_set_option(RTB_OPT_TRAJ_STORE): 0 = per-lane streaming stores, 1 = rows staged in shared memory + TMA stores
     // host-buffer calls on large fans are cut into chunks whose H2D copy, kernel and D2H copy overlap (rtb_trace)
     cudaStream_t pipe[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_ev[4] = {nullptr, nullptr, nullptr, nullptr}; // fork + one join per pipe stream
+    // the shooting refinement iterates groups of pairs on their own streams (shoot.cu)
+    static constexpr int kShootStreams = 15;
+    cudaStream_t shoot_st[kShootStreams] = {};
+    cudaEvent_t shoot_ev[kShootStreams + 1] = {};
+    int shoot_groups = 0; // rtb_set_option(RTB_OPT_SHOOT_GROUPS): 0 = auto
     // fused result gather (rtb_set_gather): peer base pointers, total rays, this rank's ray offset
     double *gather[RTB_MAX_PEERS] = {};
     int gather_world = 0;

@@ -62,6 +62,8 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     for (auto &ps : ctx->pipe) if (ps) cudaStreamDestroy(ps);
     for (auto &pe : ctx->pipe_ev) if (pe) cudaEventDestroy(pe);
+    for (auto &ps : ctx->shoot_st) if (ps) cudaStreamDestroy(ps);
+    for (auto &pe : ctx->shoot_ev) if (pe) cudaEventDestroy(pe);
     delete ctx;
 }
 
@@ -70,6 +72,7 @@ extern "C" int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value)
     if (!ctx) return RTB_ERR_ARG;
     if (option == RTB_OPT_QUEUE && value >= 0 && value <= 2) { ctx->queue_mode = value; return RTB_OK; }
     if (option == RTB_OPT_TRAJ_STORE && value >= 0 && value <= 1) { ctx->traj_mode = value; return RTB_OK; }
+    if (option == RTB_OPT_SHOOT_GROUPS && value >= 0 && value <= rtb_ctx::kShootStreams + 1) { ctx->shoot_groups = value; return RTB_OK; }
     return fail(ctx, RTB_ERR_ARG, "rtb_set_option: unknown option or value");
 }
 
@@ -323,7 +326,7 @@ int rtb_launch(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, TraceArgs a, 
     // doubles, tiles of (6*RTB_TRAJ_ROWS) x 32 and single rows of 6 x 32.  Needs 16-byte aligned rows.
     a.traj_bulk = 0;
     const int64_t rows = traj ? ((int64_t)a.max_size + a.out_stride - 1) / a.out_stride : 0;
-    if (traj && ctx->traj_mode == 0 && a.lane_shift == 0 && (a.R % 2) == 0 && ((uintptr_t)a.s_ray % 16) == 0 &&
+    if (traj && ctx->traj_mode == 1 && a.lane_shift == 0 && (a.R % 2) == 0 && ((uintptr_t)a.s_ray % 16) == 0 &&
         a.R < ((int64_t)1 << 31) && rows * 6 < ((int64_t)1 << 31)) {
         static cuTensorMapEncodeTiled_t encode = nullptr;
         if (!encode) {

@@ -14,6 +14,10 @@
 // travel time s_ray[.,4] interpolated the same way.  miss^2 = squared distance exit point - target.
 #include "ctx.cuh"
 
+#ifndef RTB_SHOOT_GROUPS_DEFAULT
+#define RTB_SHOOT_GROUPS_DEFAULT 4
+#endif
+
 namespace {
 
 struct FanBuffers { // device pointers of one batched launch
@@ -301,9 +305,10 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
     // between iterations: golden's trip count follows from the bracket width alone (the loop test RT:188 is on
     // |c - d|, which shrinks by GOLD_RATIO per pass whatever f does), so each group's count is fixed after its first
     // pass over the brackets and one counter read at the very end confirms that no pair is left iterating.
-    const int G = (int)std::min<int64_t>(4, std::max<int64_t>(1, n / 4096));
-    for (auto &ps : ctx->pipe) if (!ps) CK(cudaStreamCreateWithFlags(&ps, cudaStreamNonBlocking));
-    for (auto &pe : ctx->pipe_ev) if (!pe) CK(cudaEventCreateWithFlags(&pe, cudaEventDisableTiming));
+    const int Gwant = ctx->shoot_groups > 0 ? ctx->shoot_groups : RTB_SHOOT_GROUPS_DEFAULT;
+    const int G = (int)std::min<int64_t>(Gwant, std::max<int64_t>(1, n / 4096));
+    for (int g = 0; g + 1 < G; ++g) if (!ctx->shoot_st[g]) CK(cudaStreamCreateWithFlags(&ctx->shoot_st[g], cudaStreamNonBlocking));
+    for (int g = 0; g < G; ++g) if (!ctx->shoot_ev[g]) CK(cudaEventCreateWithFlags(&ctx->shoot_ev[g], cudaEventDisableTiming));
     unsigned long long *d_active = (unsigned long long *)sg.alloc(sizeof(unsigned long long) * 2 * G);
     struct Group { int64_t i0, n; FanBuffers fb; cudaStream_t st; int iters; };
     std::vector<Group> gr(G);
@@ -312,14 +317,14 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
         gr[g].i0 = n * g / G;
         gr[g].n = n * (g + 1) / G - gr[g].i0;
         gr[g].fb = alloc_fan(sg, 2 * gr[g].n);
-        gr[g].st = g == 0 ? st : ctx->pipe[g - 1];
+        gr[g].st = g == 0 ? st : ctx->shoot_st[g - 1];
         gr[g].iters = 0;
         ok = sg.err == cudaSuccess && gr[g].fb.exit_out;
     }
     if (!ok) return fail(ctx, RTB_ERR_NOMEM, "rtb_shoot_refine: staging", sg.err);
     auto bail = [&](int code) {
         cudaStreamSynchronize(st);
-        for (auto &ps : ctx->pipe) cudaStreamSynchronize(ps);
+        for (auto &ps : ctx->shoot_st) if (ps) cudaStreamSynchronize(ps);
         return code;
     };
     CK(cudaMemsetAsync(ctx->d_total, 0, 2 * sizeof(unsigned long long), st));
@@ -348,8 +353,8 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
         iters = std::max<int64_t>(iters, k);
     }
     // fork: the side streams start after the brackets are initialised
-    CK(cudaEventRecord(ctx->pipe_ev[0], st));
-    for (int g = 1; g < G; ++g) CK(cudaStreamWaitEvent(gr[g].st, ctx->pipe_ev[0], 0));
+    CK(cudaEventRecord(ctx->shoot_ev[0], st));
+    for (int g = 1; g < G; ++g) CK(cudaStreamWaitEvent(gr[g].st, ctx->shoot_ev[0], 0));
     CK(cudaMemsetAsync(d_active, 0, sizeof(unsigned long long) * 2 * G, st));
     int max_it = 0;
     for (auto &k : gr) max_it = std::max(max_it, k.iters);
@@ -367,8 +372,8 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
     }
     // join
     for (int g = 1; g < G; ++g) {
-        CK(cudaEventRecord(ctx->pipe_ev[g], gr[g].st));
-        CK(cudaStreamWaitEvent(st, ctx->pipe_ev[g], 0));
+        CK(cudaEventRecord(ctx->shoot_ev[g], gr[g].st));
+        CK(cudaStreamWaitEvent(st, ctx->shoot_ev[g], 0));
     }
     CK(cudaMemcpyAsync(h_active.data(), d_active, sizeof(unsigned long long) * 2 * G, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));

@@ -6,7 +6,8 @@
 //
 // Two kernels share the per-ray code (ray_init / ray_step / ray_finish):
 //   trace_kernel        static mapping thread <-> ray.  Every output mode; the only one that writes trajectories:
-//                       rows are staged per warp in shared memory and leave as 2-D TMA stores, one per tile of
+//                       per-lane streaming stores (a warp's 32 doubles of one (row, column) are one 256-byte segment),
+//                       or rows staged per warp in shared memory that leave as 2-D TMA stores, one per tile of
 //                       RTB_TRAJ_ROWS rows x 6 columns x 32 rays (cp.async.bulk.tensor shared -> global; traj_stage.cuh);
 //   trace_queue_kernel  persistent warps that pull rays from a global queue (atomic counter): when lanes of a warp
 //                       have finished their rays (RT:878 break, or per-ray max_size) the warp compacts -- the dead
@@ -359,7 +360,7 @@ trace_kernel(const __grid_constant__ TraceArgs a)
         if (alive) {
             alive = ray_step<METHOD, ISO, TRAJ, EXACT, EXTRA, LAZY>(a, r, gamma, g2m1, q, i, mask, wbuf);
             if (TMODE == 1 && i == next_keep) { // per-lane stores need no convergence: each lane writes its own row
-                tw.row(true, q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
+                tw.row_live(q.s.x, q.s.y, q.px, q.py, q.T, q.s.ang);
                 next_keep += a.out_stride;
             }
         } else if (TMODE == 1) {

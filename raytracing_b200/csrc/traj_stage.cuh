@@ -9,8 +9,13 @@
 //              (6*RTB_TRAJ_ROWS) x 32 at (row*6, first ray of the warp).  Rays past the end of the fan are clipped by
 //              the tensor map.  (Per-segment 1-D bulk copies would not do: UBLKCP takes warp-uniform addresses, so 24
 //              lanes issuing one each are serialised into 24 issue rounds -- tools/hbm_write_microbench.cu.)
-// The staged path needs 16-byte aligned rows (R even, s_ray 16-byte aligned) and one ray per lane; rtb_launch picks it
-// when that holds (TraceArgs.traj_bulk) and encodes the two tensor maps; small spread fans keep the per-lane stores.
+// The staged path needs 16-byte aligned rows (R even, s_ray 16-byte aligned) and one ray per lane; rtb_launch encodes the
+// two tensor maps when it is asked for (RTB_OPT_TRAJ_STORE 1).  Measured on the 45.8 GB fisheye trajectory it is 5-7 %
+// SLOWER than the per-lane stores: the write-back was never limited by the store instructions --
+// a bare store kernel with this access pattern reaches the HBM copy peak either way (tools/hbm_write_microbench.cu) --
+// but by the instruction count of the step loop, and the proxy fence + warp synchronisation of every flush cost more
+// than the per-column address additions they replace.  So the per-lane path is the default and the staged one is kept
+// selectable, bit-identical, for parts where the load/store pipe is the limiter.
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -38,35 +43,47 @@ template <int MODE> struct TrajWriter;
 template <> struct TrajWriter<0> {
     __device__ __forceinline__ void init(double *, const TrajMaps *, int64_t, int64_t, bool, unsigned char *) {}
     __device__ __forceinline__ void row(bool, double, double, double, double, double, double) {}
+    __device__ __forceinline__ void row_live(double, double, double, double, double, double) {}
     __device__ __forceinline__ void zero_tail(int, bool) {}
     __device__ __forceinline__ void ended() {}
     __device__ __forceinline__ void finish() {}
 };
 
 template <> struct TrajWriter<1> { // per-lane stores
-    double *gp; // this lane's entry of the next row
-    int64_t R;
+    char *gp;    // this lane's entry of the next row
+    int64_t Rb;  // bytes from one column to the next: 8 R.  The six column addresses of a row and the next row's first
+                 // are formed by repeated 64-bit addition (12 instructions per row; indexing gp[c * R] costs 27)
     bool valid;
-    __device__ __forceinline__ void init(double *s_ray, const TrajMaps *, int64_t R_, int64_t r, bool valid_, unsigned char *)
+    __device__ __forceinline__ void init(double *s_ray, const TrajMaps *, int64_t R, int64_t r, bool valid_, unsigned char *)
     {
-        R = R_; valid = valid_; gp = s_ray + r;
+        Rb = R * (int64_t)sizeof(double); valid = valid_; gp = reinterpret_cast<char *>(s_ray + r);
     }
+    __device__ __forceinline__ void put(double x, double yv, double px, double py, double T, double ang)
+    {
+        char *p = gp;
+        __stcs(reinterpret_cast<double *>(p), x); p += Rb;
+        __stcs(reinterpret_cast<double *>(p), yv); p += Rb;
+        __stcs(reinterpret_cast<double *>(p), px); p += Rb;
+        __stcs(reinterpret_cast<double *>(p), py); p += Rb;
+        __stcs(reinterpret_cast<double *>(p), T); p += Rb;
+        __stcs(reinterpret_cast<double *>(p), ang);
+        gp = p + Rb;
+    }
+    // a row of a stepping ray (`live`: the lane is valid by construction) or, for a lane whose ray has ended, zeros
+    // when the caller wants the tail written (store)
     __device__ __forceinline__ void row(bool store, double x, double yv, double px, double py, double T, double ang)
     {
-        if (valid && store) {
-            __stcs(gp, x); __stcs(gp + R, yv); __stcs(gp + 2 * R, px);
-            __stcs(gp + 3 * R, py); __stcs(gp + 4 * R, T); __stcs(gp + 5 * R, ang);
-        }
-        gp += 6 * R;
+        if (valid && store) put(x, yv, px, py, T, ang);
+        else gp += 6 * Rb;
+    }
+    __device__ __forceinline__ void row_live(double x, double yv, double px, double py, double T, double ang)
+    {
+        put(x, yv, px, py, T, ang);
     }
     __device__ __forceinline__ void zero_tail(int n, bool tail_zero)
     {
         if (valid && tail_zero)
-            for (int j = 0; j < n; ++j) {
-                __stcs(gp, 0.0); __stcs(gp + R, 0.0); __stcs(gp + 2 * R, 0.0);
-                __stcs(gp + 3 * R, 0.0); __stcs(gp + 4 * R, 0.0); __stcs(gp + 5 * R, 0.0);
-                gp += 6 * R;
-            }
+            for (int j = 0; j < n; ++j) put(0.0, 0.0, 0.0, 0.0, 0.0, 0.0);
     }
     __device__ __forceinline__ void ended() {}
     __device__ __forceinline__ void finish() {}
@@ -144,6 +161,11 @@ template <> struct TrajWriter<2> { // staged rows + TMA stores
             b[0] = x; b[32] = yv; b[64] = px; b[96] = py; b[128] = T; b[160] = ang;
         }
         if (++k == RTB_TRAJ_ROWS) { flush(RTB_TRAJ_ROWS); k = 0; }
+    }
+
+    __device__ __forceinline__ void row_live(double x, double yv, double px, double py, double T, double ang)
+    {
+        row(true, x, yv, px, py, T, ang);
     }
 
     // This lane's ray has just stored its last row: the rows of the current tile it will not reach are cleared now

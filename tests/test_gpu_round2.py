@@ -180,7 +180,7 @@ def test_tma_trajectory_store_equals_per_lane(engine, uc, m, R, M, stride, tail_
     th, x0, y0 = rt.make_fan(uc, R)
     rows = (M + stride - 1) // stride
     out = []
-    for mode in (1, 0):          # per-lane stores first, then the staged path (odd R: both runs take the per-lane path)
+    for mode in (0, 1):          # per-lane stores first, then the staged path (odd R: both runs take the per-lane path)
         engine.set_option("traj_store", mode)
         buf = torch.zeros(rows, 6, R, dtype=torch.float64, device="cuda") if not tail_zero else \
             torch.full((rows, 6, R), -3.0, dtype=torch.float64, device="cuda")

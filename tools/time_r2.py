@@ -69,7 +69,7 @@ a = fan(uc, 20)
 M = rt.max_size_for(uc, rt.DELTA_S, 91)
 s_ray = torch.empty(M, 6, 1 << 20, dtype=torch.float64, device=dev)
 for m in (6, 1):
-    for mode, name in ((1, "per-lane st.global"), (0, "staged + TMA store")):
+    for mode, name in ((0, "per-lane st.global"), (1, "staged + TMA store")):
         eng.set_option("traj_store", mode)
         ms, steps = best(lambda: eng.trace(m, *a, rt.DELTA_S, M, c[0], c[5:9], full=True, out=dict(s_ray=s_ray)))
         print("fisheye 2^20 op%d FULL %s %9.3f ms  %.4e ray-steps/s  %.0f GB/s" % (m, name, ms, steps / ms * 1e3, steps * 48 / ms / 1e6),
