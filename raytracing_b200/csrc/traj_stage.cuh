@@ -168,12 +168,13 @@ template <> struct TrajWriter<2> { // staged rows + TMA stores
         row(true, x, yv, px, py, T, ang);
     }
 
-    // This lane's ray has just stored its last row: the rows of the current tile it will not reach are cleared now
-    // (the previous flush has finished reading them: reads_done ran when this tile was begun), the rest of its column
-    // at the start of the next tile.
+    // This lane's ray has just stored its last row.  The rows of the current tile it will not reach are cleared now:
+    // they were last read by the previous flush, and reads_done ran when this tile was begun.  With k == 0 the row
+    // just stored completed a tile whose TMA store is in flight and still reading the slice -- nothing may be
+    // touched; the whole column is cleared at the start of the next tile, after reads_done (zero_pending).
     __device__ __forceinline__ void ended()
     {
-        clear_rows(k);
+        if (k > 0) clear_rows(k);
         zero_pending = true;
     }
 

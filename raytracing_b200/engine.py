@@ -107,12 +107,17 @@ class Engine:
             raise _cabi.RtbError(rc, self._lib.rtb_last_error(self._ctx).decode())
 
     def use_torch_stream(self):
-        """Launch on torch's current stream so torch.cuda.Event timing brackets the kernels."""
+        """Launch on torch's current stream: torch.cuda.Event timing brackets the kernels, and the library's work is
+        ordered after whatever torch has queued on the caller's tensors (a torch.zeros(...) passed as `out`, say).
+        Every call that takes torch tensors does this itself."""
         import torch
         h = torch.cuda.current_stream(self.device).cuda_stream
         # torch's default stream has handle 0, which rtb_set_stream reads as "own stream": pass the
         # explicit legacy-default-stream handle (cudaStreamLegacy == 0x1) instead
-        self._check(self._lib.rtb_set_stream(self._ctx, C.c_void_p(h if h else 1)))
+        h = h if h else 1
+        if getattr(self, "_torch_stream", None) != h:
+            self._check(self._lib.rtb_set_stream(self._ctx, C.c_void_p(h)))
+            self._torch_stream = h
 
     def set_field(self, z, grd):
         """Upload z (bilinear n) and grd = (dn/dy spline, dn/dx spline) as interpolacion() returns
@@ -139,6 +144,7 @@ class Engine:
         x, y, Z = fit["x"], fit["y"], fit["Z"]
         stats = _cabi.RtbStats()
         if _is_torch(Z):
+            self.use_torch_stream()
             kind, ptrs = _cabi.RTB_PTR_DEVICE, (y.data_ptr(), x.data_ptr(), Z.data_ptr())
         else:
             kind, ptrs = _cabi.RTB_PTR_HOST, (y.ctypes.data, x.ctypes.data, Z.ctypes.data)
@@ -279,6 +285,7 @@ class Engine:
             want_errors = bool(interface)
         if dev:
             import torch
+            self.use_torch_stream()
             R = theta0.numel()
             f64 = dict(dtype=torch.float64, device=theta0.device)
             def prep(a):
@@ -331,6 +338,7 @@ class Engine:
         dev = _is_torch(like)
         if dev:
             import torch
+            self.use_torch_stream()
             f64 = lambda a: a.contiguous() if _is_torch(a) else torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).to(like.device)
             i64 = lambda a: a if _is_torch(a) else torch.as_tensor(np.ascontiguousarray(a, dtype=np.int64)).to(like.device)
             ptr = lambda a: C.c_void_p(a.data_ptr()) if a is not None else None

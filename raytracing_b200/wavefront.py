@@ -26,6 +26,7 @@ def wavefront_points(s_ray, d_ray, times=DEFAULT_TIMES, engine=None):
     assert six == 6
     if dev:
         import torch
+        eng.use_torch_stream()
         times_a = torch.as_tensor(np.ascontiguousarray(times, dtype=np.float64)).to(s_ray.device)
         out = torch.empty(4, times_a.numel(), R, dtype=torch.float64, device=s_ray.device)
         ptr = lambda a: C.c_void_p(a.data_ptr())

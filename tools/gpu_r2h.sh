@@ -1,0 +1,6 @@
+#!/bin/bash
+# Round 2, call H (1 GPU): tests, FULL-mode A/B with the pointer-increment stores.
+O=gpurun_out/r2h; mkdir -p $O
+timeout 1500 python -m pytest tests -m gpu -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.log
+grep -E "passed|failed|FAILED|Error|rc=" $O/pytest_gpu.log | head -20
+timeout 600 python tools/time_r2.py 2>&1 | grep -E "FULL" > $O/time_r2.log; cat $O/time_r2.log
