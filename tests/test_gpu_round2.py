@@ -167,6 +167,21 @@ def test_ray_queue_equals_static_grid(engine, case):
         assert bool((a.d_ray[2][::97] == 0).all())
 
 
+def test_sort_fan_gives_the_same_results(engine):
+    """Engine.trace(sort_fan=True): an unsorted fan traced in sorted order, results handed back in the caller's order."""
+    import torch
+    s = scenario_setup("3")
+    engine.set_field(s["z"], s["grd"])
+    R = (1 << 16) + 5
+    th, x0, y0 = rt.make_fan("3", R)
+    th = np.random.default_rng(11).permutation(th)
+    kw = dict(full=False, want_px_stats=True)
+    a = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], **kw)
+    b = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], sort_fan=True, **kw)
+    for name in ("d_ray", "last_row", "px_stats"):
+        assert torch.equal(torch.nan_to_num(a[name], nan=-1.0), torch.nan_to_num(b[name], nan=-1.0)), name
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # Trajectory rows staged in shared memory + 2-D TMA stores == per-lane stores, bit for bit
 # ------------------------------------------------------------------------------------------------------------------

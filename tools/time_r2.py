@@ -4,6 +4,7 @@
 """
 import os
 import sys
+import time
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import numpy as np
@@ -44,6 +45,20 @@ for uc, lg, m, kw, tag in (("2", 20, 6, {}, "fisheye 2^20 op6 final"), ("2", 20,
         ms, steps = best(lambda: eng.trace(m, *a, rt.DELTA_S, M, c[0], c[5:9], full=False, **kw))
         print("%-32s %s %9.3f ms  %.4e ray-steps/s" % (tag, name, ms, steps / ms * 1e3), flush=True)
 eng.set_option("queue", 0)
+
+# the remedy for an unsorted fan: trace it in sorted order (Engine.trace(sort_fan=True): torch.sort + gather + scatter)
+uc = "3"
+eng.set_field(*rt.build_field(uc))
+c = rt.scenario_constants(uc)
+a = fan(uc, 20, True)
+M = rt.max_size_for(uc, rt.DELTA_S, 91)
+for name, kw in (("as given ", {}), ("sort_fan ", dict(sort_fan=True))):
+    for _ in range(2):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        r = eng.trace(6, *a, rt.DELTA_S, M, c[0], c[5:9], full=False, **kw)
+        torch.cuda.synchronize(); dt = time.perf_counter() - t0
+    print("%-32s %s %9.3f ms wall (kernel %.3f)  %.4e ray-steps/s" % ("vert 2^20 op6 SHUFFLED", name, dt * 1e3, r.stats["kernel_ms"],
+                                                                       r.stats["ray_steps"] / dt), flush=True)
 
 # mixed DELTA_S candidates inside every warp (per-ray step / max_size): where lanes of one warp differ widely in length
 uc = "3"
