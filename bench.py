@@ -231,16 +231,16 @@ class Dist:
         return mx.tolist(), sm.tolist()
 
 
-def load_ncu_latest(build_id):
-    """Executed-instruction counts of the kernels, from the ncu captures tools/ncu_summary.py --json condensed into
-    profiles/ncu_latest.json.  They describe one build of the kernels: used only when its build id (digest of the CUDA
-    sources, rtb_build_id) is the loaded library's, so the numbers are traceable to a capture of THIS code."""
+def load_ncu_latest(kernel_id):
+    """Executed-instruction counts of the kernels, from the ncu captures tools/ncu_summary.py json condensed into
+    profiles/ncu_latest.json.  They describe one version of the trace kernels: used only when its kernel id (digest of
+    the kernel sources, rtb_kernel_id) is the loaded library's, so the numbers are traceable to a capture of THIS code."""
     try:
         d = json.load(open(os.path.join(ROOT, "profiles", "ncu_latest.json")))
     except (OSError, ValueError):
         return None, "profiles/ncu_latest.json missing"
-    if d.get("build_id") != build_id:
-        return None, "profiles/ncu_latest.json is of build %s, the library is %s" % (d.get("build_id"), build_id)
+    if d.get("kernel_id") != kernel_id:
+        return None, "profiles/ncu_latest.json is of kernels %s, the library's are %s" % (d.get("kernel_id"), kernel_id)
     return d, None
 
 
@@ -404,7 +404,7 @@ def run_cuda(args):
         [t_ms, e2e_ms, float(ray_steps), float(e2e_steps), float(launches)])
     ray_steps, e2e_steps, launches = int(ray_steps), int(e2e_steps), int(launches)
 
-    ncu, ncu_note = load_ncu_latest(eng.build_id())
+    ncu, ncu_note = load_ncu_latest(eng.kernel_id())
     ctx = dict(D=D, eng=eng, rt=rt, K=K, args=args, fp64_peak=fp64_peak, ncu=ncu, ncu_note=ncu_note)
     configs = run_secondary_configs(ctx) if args.configs == "all" else None
 
@@ -425,7 +425,7 @@ def run_cuda(args):
                            "rays_per_gpu": R, "max_size": M, "ray_steps_per_step": ray_steps // args.steps,
                            "l2": "flushed (256 MiB write) between timed steps",
                            "parallelism": ("rays sharded x%d, d_ray gathered on every GPU: %s" % (world, gather_mode))
-                           if world > 1 else "1 GPU", "build_id": eng.build_id()},
+                           if world > 1 else "1 GPU", "build_id": eng.build_id(), "kernel_id": eng.kernel_id()},
                 "roofline": roofline_block(METHOD, "trace_kernel<6,iso,final>", per_gpu_steps, k_ms, fp64_peak,
                                            (clocks or {}).get("sm_mhz"), ncu, ncu_note, "op6_final_fisheye", K.F_ALG),
                 "e2e": {"value": e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,

@@ -112,6 +112,9 @@ int rtb_abi_version(void);
 /* Hex digest of the CUDA sources the library was compiled from (written by csrc/Makefile): lets a caller check that a
    prebuilt librtb.so matches the source tree it sits in. */
 const char *rtb_build_id(void);
+/* The same for the sources of the trace kernels alone: identifies the kernels an ncu capture (profiles/ncu_latest.json)
+   was taken of, whatever changed on the host side of the library. */
+const char *rtb_kernel_id(void);
 /* Tuning / test switches of a context.  RTB_OPT_QUEUE: 0 = per call (RTB_F_RAY_QUEUE / RTB_F_STATIC_GRID; default static),
    1 = always where possible, 2 = never (static grid).  RTB_OPT_TRAJ_STORE: 0 = per-lane st.global.cs (default: faster
    on B200), 1 = trajectory rows staged in shared memory, 2-D TMA stores (needs R even). */

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace rtb {
@@ -49,6 +50,11 @@ struct rtb_ctx {
     cudaStream_t shoot_st[kShootStreams] = {};
     cudaEvent_t shoot_ev[kShootStreams + 1] = {};
     int shoot_groups = 0; // rtb_set_option(RTB_OPT_SHOOT_GROUPS): 0 = auto
+    // pinned bounce buffers of the large pageable device-to-host copies (Staging::copy_back)
+    static constexpr int kBounce = 3;
+    static constexpr size_t kBounceBytes = (size_t)64 << 20;
+    void *bounce[kBounce] = {};
+    cudaEvent_t bounce_ev[kBounce] = {};
     // fused result gather (rtb_set_gather): peer base pointers, total rays, this rank's ray offset
     double *gather[RTB_MAX_PEERS] = {};
     int gather_world = 0;
@@ -192,9 +198,56 @@ struct Staging {
         back.push_back({p + col0, d, cols * sizeof(T), rows, pitch * sizeof(T), cols * sizeof(T)});
         return (T *)d;
     }
+    // A large result going to PAGEABLE host memory (the drop-in trazar() returns a fresh numpy array: 45.8 GB for the
+    // 2^20-ray fisheye fan).  cudaMemcpy stages such a copy through the driver's own pinned buffer on one host thread and
+    // takes the first-touch page faults of the fresh array on that same thread (measured 4 GB/s).  Here the copy is cut
+    // into 64 MB chunks that DMA into three pinned bounce buffers while a team of host threads moves -- and first-touches --
+    // the previous chunk into the caller's array.
+    bool copy_back_pageable(void *host, const void *dev, size_t bytes)
+    {
+        for (int k = 0; k < rtb_ctx::kBounce; ++k) {
+            if (!ctx->bounce[k] && cudaMallocHost(&ctx->bounce[k], rtb_ctx::kBounceBytes) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+            if (!ctx->bounce_ev[k] && cudaEventCreateWithFlags(&ctx->bounce_ev[k], cudaEventDisableTiming) != cudaSuccess) return false;
+        }
+        const size_t CH = rtb_ctx::kBounceBytes;
+        const size_t nch = (bytes + CH - 1) / CH;
+        const unsigned hw = std::thread::hardware_concurrency();
+        const int T = (int)std::max(1u, std::min(16u, hw ? hw : 4u));
+        auto issue = [&](size_t i) {
+            const size_t off = i * CH, n = std::min(CH, bytes - off);
+            const int k = (int)(i % rtb_ctx::kBounce);
+            cudaError_t e = cudaMemcpyAsync(ctx->bounce[k], (const char *)dev + off, n, cudaMemcpyDeviceToHost, stream);
+            if (e == cudaSuccess) e = cudaEventRecord(ctx->bounce_ev[k], stream);
+            if (e != cudaSuccess) err = e;
+        };
+        for (size_t i = 0; i < std::min<size_t>(nch, rtb_ctx::kBounce); ++i) issue(i);
+        for (size_t i = 0; i < nch && err == cudaSuccess; ++i) {
+            const size_t off = i * CH, n = std::min(CH, bytes - off);
+            const int k = (int)(i % rtb_ctx::kBounce);
+            cudaError_t e = cudaEventSynchronize(ctx->bounce_ev[k]);
+            if (e != cudaSuccess) { err = e; break; }
+            std::vector<std::thread> team;
+            const size_t per = ((n + T - 1) / T + 4095) & ~(size_t)4095;
+            for (int t = 0; t < T; ++t) {
+                const size_t a = std::min(n, (size_t)t * per), b = std::min(n, a + per);
+                if (b > a) team.emplace_back([=] { std::memcpy((char *)host + off + a, (const char *)ctx->bounce[k] + a, b - a); });
+            }
+            for (auto &th : team) th.join();
+            if (i + rtb_ctx::kBounce < nch) issue(i + rtb_ctx::kBounce);
+        }
+        d2h += (int64_t)bytes;
+        return err == cudaSuccess;
+    }
     void copy_back()
     {
         for (auto &b : back) {
+            if (b.rows == 1 && b.bytes >= ((size_t)256 << 20)) { // large and contiguous: pageable destination?
+                cudaPointerAttributes at;
+                const bool pageable = cudaPointerGetAttributes(&at, b.host) != cudaSuccess || at.type == cudaMemoryTypeUnregistered;
+                (void)cudaGetLastError();
+                if (pageable && copy_back_pageable(b.host, b.dev, b.bytes)) continue;
+                if (err != cudaSuccess) return;
+            }
             cudaError_t e = b.rows == 1
                 ? cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, stream)
                 : cudaMemcpy2DAsync(b.host, b.host_pitch, b.dev, b.dev_pitch, b.bytes, b.rows, cudaMemcpyDeviceToHost, stream);

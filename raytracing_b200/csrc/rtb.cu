@@ -16,6 +16,8 @@ extern "C" int rtb_abi_version(void) { return RTB_ABI_VERSION; }
 // stale librtb.so cannot pass for the current code.
 #include "build_id.h"
 extern "C" const char *rtb_build_id(void) { return RTB_BUILD_ID; }
+// Digest of the trace-kernel sources alone (tools/build_id.py KERNEL_SOURCES): the key of profiles/ncu_latest.json.
+extern "C" const char *rtb_kernel_id(void) { return RTB_KERNEL_ID; }
 
 extern "C" const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
@@ -62,6 +64,8 @@ extern "C" void rtb_destroy(rtb_ctx *ctx)
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     for (auto &ps : ctx->pipe) if (ps) cudaStreamDestroy(ps);
     for (auto &pe : ctx->pipe_ev) if (pe) cudaEventDestroy(pe);
+    for (auto &bb : ctx->bounce) if (bb) cudaFreeHost(bb);
+    for (auto &be : ctx->bounce_ev) if (be) cudaEventDestroy(be);
     for (auto &ps : ctx->shoot_st) if (ps) cudaStreamDestroy(ps);
     for (auto &pe : ctx->shoot_ev) if (pe) cudaEventDestroy(pe);
     delete ctx;

@@ -231,6 +231,9 @@ class Engine:
     def build_id(self):
         return self._lib.rtb_build_id().decode()
 
+    def kernel_id(self):
+        return self._lib.rtb_kernel_id().decode()
+
     def sweep(self, method, theta0, x0, y0, steps, max_sizes, gamma, box, metric, skip_lo=0, skip_hi=0, exact=False):
         """rtb_sweep: the DELTA_S sweep (RT_bench.py:1303-1318) as batched traces of candidates x rays with the
         per-candidate reductions on the device.  metric: "snell" | "closure" | "px_cv".  numpy in, numpy out:

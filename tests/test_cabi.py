@@ -71,3 +71,4 @@ def test_library_was_built_from_this_tree():
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import build_id
     assert _cabi.load().rtb_build_id().decode() == build_id.digest()
+    assert _cabi.load().rtb_kernel_id().decode() == build_id.kernel_digest()

@@ -4,8 +4,8 @@
   ncu_summary.py json OUT.json KEY=PREFIX [KEY=PREFIX..]  profiles/ncu_latest.json: per kernel the executed FP64
         instructions per ray-step, instructions per warp-step, pipe utilisations and DRAM bytes of the capture
         PREFIX.raw.csv, normalised by the ray-step count PREFIX.plain.log reports (tools/prof_trace.py prints
-        `... ray_steps=N`).  Stamped with the digest of the CUDA sources (tools/build_id.py = rtb_build_id() of the
-        library that was profiled), so bench.py only uses it for the build it describes.
+        `... ray_steps=N`).  Stamped with the digest of the trace-kernel sources (tools/build_id.py kernel_digest =
+        rtb_kernel_id() of the library that was profiled), so bench.py only uses it for the kernels it describes.
 """
 import csv
 import json
@@ -70,13 +70,13 @@ def kernel_entry(prefix, key):
 def to_json(out, pairs):
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     import build_id
-    d = {"build_id": build_id.digest(), "how": "ncu --set full --clock-control none, one launch per kernel after warm-up "
+    d = {"kernel_id": build_id.kernel_digest(), "how": "ncu --set full --clock-control none, one launch per kernel after warm-up "
          "launches (tools/gpu_*.sh); per ray-step = thread instructions / ray-steps of the launch", "kernels": {}}
     for p in pairs:
         key, prefix = p.split("=", 1)
         d["kernels"][key] = kernel_entry(prefix, key)
     json.dump(d, open(out, "w"), indent=1)
-    print("wrote", out, "build", d["build_id"], "kernels", list(d["kernels"]))
+    print("wrote", out, "kernel_id", d["kernel_id"], "kernels", list(d["kernels"]))
 
 
 if __name__ == "__main__":
