@@ -137,10 +137,14 @@ struct GoldenBracket {
 
 // Evaluating search (anisotropic cost; isotropic cost when the turn is too large for golden_iso_sym).  State of a pass:
 // the kept probe W and the newest probe N (sin, cos, cost), on which side N lies, and the bracket midpoint - theta.
+// Sides and decisions are sign masks (0 or 0x80000000), so a pass takes them from and applies them to the high words
+// of its doubles with integer logic: no FP64 compare, no 64-bit select for a sign.
 struct TrigState {
     double Ws, Wc, Wf, Ns, Nc, Nf, m;
-    bool nl; // N is the left probe (c)
+    int nl; // sign mask: N is the left probe (c)
 };
+
+#define RTB_SIGN ((int)0x80000000)
 
 template <class F>
 __device__ __forceinline__ void trig_init(const F &cost, double st, double ct, TrigState &g)
@@ -150,7 +154,7 @@ __device__ __forceinline__ void trig_init(const F &cost, double st, double ct, T
     g.Ws = fma(-ct, S0, st * C0); g.Wc = fma(st, S0, ct * C0);
     g.Ns = fma(ct, S0, st * C0); g.Nc = fma(-st, S0, ct * C0);
     g.Wf = cost(g.Ws, g.Wc); g.Nf = cost(g.Ns, g.Nc);
-    g.nl = false;
+    g.nl = 0;
     g.m = 0.0;
 }
 
@@ -162,22 +166,24 @@ __device__ __forceinline__ bool trig_in_band(const TrigState &g, double tie2, do
     return __double2hiint(df * df) <= __double2hiint(tie2 * (g.Nf + g.Wf));
 }
 
-// RT:189 `if func(c) < func(d)` from the sign of f(N) - f(W): c is N when nl
-__device__ __forceinline__ bool trig_decide(const TrigState &g, double df) { return (__double2hiint(df) < 0) == g.nl; }
+// RT:189 `if func(c) < func(d)` as a sign mask, from the sign of f(N) - f(W): c is N when nl, so
+// left <=> (df < 0) == nl <=> the sign bits of df and nl agree.
+__device__ __forceinline__ int trig_decide(const TrigState &g, double df)
+{
+    return ((__double2hiint(df) ^ g.nl) & RTB_SIGN) ^ RTB_SIGN;
+}
 
-// After the decision of pass k: the kept probe (c when b moves, d when a moves), the midpoint move, and the new probe
-// at the kept one -+ pi rho^(k+4): one rotation by table constants, one cost evaluation.  Signs by integer transfer.
+// After the decision of pass k (`left`: sign mask): the kept probe (c when b moves, d when a moves), the midpoint move,
+// and the new probe at the kept one -+ pi rho^(k+4): one rotation by table constants, one cost evaluation.
 template <class F>
-__device__ __forceinline__ void trig_advance(const F &cost, TrigState &g, bool left, int k)
+__device__ __forceinline__ void trig_advance(const F &cost, TrigState &g, int left, int k)
 {
     if (left == g.nl) { g.Ws = g.Ns; g.Wc = g.Nc; g.Wf = g.Nf; }
-    const int sgn = left ? (int)0x80000000 : 0;
-    const double q = kGoldenMid[k];
-    g.m += __hiloint2double(__double2hiint(q) ^ sgn, __double2loint(q)); // left: the midpoint moves by -q
-    const double2 r = kGoldenRot[k];
-    const double sr = __hiloint2double(__double2hiint(r.x) ^ sgn, __double2loint(r.x)); // the new probe lies left of the kept one when b moved
-    g.Ns = fma(g.Wc, sr, g.Ws * r.y);
-    g.Nc = fma(-g.Ws, sr, g.Wc * r.y);
+    const GoldenPass t = kGoldenPass[k];
+    g.m += __hiloint2double(__double2hiint(t.mid) ^ left, __double2loint(t.mid)); // left: the midpoint moves by -mid
+    const double sr = __hiloint2double(__double2hiint(t.sr) ^ left, __double2loint(t.sr)); // the new probe lies left of the kept one when b moved
+    g.Ns = fma(g.Wc, sr, g.Ws * t.cr);
+    g.Nc = fma(-g.Ws, sr, g.Wc * t.cr);
     g.Nf = cost(g.Ns, g.Nc);
     g.nl = left;
 }
@@ -196,11 +202,11 @@ static __device__ __noinline__ bool golden_trig_tie(const F cost, const TIE t, d
     trig_init(cost, st, ct, g);
     for (int j = 0;; ++j) {
         double df;
-        bool left;
-        if (trig_in_band(g, tie2, df)) left = cf(br.c) < cf(br.d); // RT:189
+        int left;
+        if (trig_in_band(g, tie2, df)) left = cf(br.c) < cf(br.d) ? RTB_SIGN : 0; // RT:189
         else left = trig_decide(g, df);
-        if (j == k) return left;
-        br.shrink(left);
+        if (j == k) return left != 0;
+        br.shrink(left != 0);
         trig_advance(cost, g, left, j);
     }
 }
@@ -225,7 +231,7 @@ __device__ __forceinline__ double golden_trig(const F &cost, const TIE &ref, dou
         }
         if (!band) break;
         const bool left = golden_trig_tie(cost, ref, tie2, theta, st, ct, k);
-        trig_advance(cost, g, left, k);
+        trig_advance(cost, g, left ? RTB_SIGN : 0, k);
         ++k;
     }
     // (a+b)/2 lies half a probe distance from the kept probe: to its left when the kept probe is d (N is c)
