@@ -121,6 +121,8 @@ const char *rtb_kernel_id(void);
 #define RTB_OPT_QUEUE 1
 #define RTB_OPT_TRAJ_STORE 2
 #define RTB_OPT_SHOOT_GROUPS 3 /* rtb_shoot_refine: groups of pairs iterating on their own streams, 1..16; 0 = auto */
+#define RTB_OPT_SHOOT_SPECULATE 4 /* rtb_shoot_refine: two golden passes per launch (both outcomes of a pass are traced
+                                     before it is decided): 0 / 1 = off (default: it is slower on every problem measured), 2 = on; same results */
 int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value);
 
 /*

@@ -8,7 +8,7 @@ LIB_PATH = os.environ.get("RTB_LIB_PATH") or os.path.join(_HERE, "csrc", "librtb
 
 RTB_PTR_HOST, RTB_PTR_DEVICE = 0, 1
 RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO, RTB_F_STATIC_GRID, RTB_F_RAY_QUEUE = 1, 2, 4, 8, 16
-RTB_OPT_QUEUE, RTB_OPT_TRAJ_STORE, RTB_OPT_SHOOT_GROUPS = 1, 2, 3
+RTB_OPT_QUEUE, RTB_OPT_TRAJ_STORE, RTB_OPT_SHOOT_GROUPS, RTB_OPT_SHOOT_SPECULATE = 1, 2, 3, 4
 RTB_SWEEP_SNELL, RTB_SWEEP_CLOSURE, RTB_SWEEP_PX_CV = 1, 2, 3
 RTB_ABI_VERSION = 2
 RTB_OK, RTB_ERR_ARG, RTB_ERR_CUDA, RTB_ERR_NOFIELD, RTB_ERR_NOMEM = 0, -1, -2, -3, -4

@@ -50,6 +50,7 @@ struct rtb_ctx {
     cudaStream_t shoot_st[kShootStreams] = {};
     cudaEvent_t shoot_ev[kShootStreams + 1] = {};
     int shoot_groups = 0; // rtb_set_option(RTB_OPT_SHOOT_GROUPS): 0 = auto
+    int shoot_spec = 0;   // rtb_set_option(RTB_OPT_SHOOT_SPECULATE): 0 = auto, 1 = off, 2 = on
     // pinned bounce buffers of the large pageable device-to-host copies (Staging::copy_back)
     static constexpr int kBounce = 3;
     static constexpr size_t kBounceBytes = (size_t)64 << 20;

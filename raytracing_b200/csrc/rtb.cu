@@ -76,6 +76,7 @@ extern "C" int rtb_set_option(rtb_ctx *ctx, int32_t option, int32_t value)
     if (!ctx) return RTB_ERR_ARG;
     if (option == RTB_OPT_QUEUE && value >= 0 && value <= 2) { ctx->queue_mode = value; return RTB_OK; }
     if (option == RTB_OPT_TRAJ_STORE && value >= 0 && value <= 1) { ctx->traj_mode = value; return RTB_OK; }
+    if (option == RTB_OPT_SHOOT_SPECULATE && value >= 0 && value <= 2) { ctx->shoot_spec = value; return RTB_OK; }
     if (option == RTB_OPT_SHOOT_GROUPS && value >= 0 && value <= rtb_ctx::kShootStreams + 1) { ctx->shoot_groups = value; return RTB_OK; }
     return fail(ctx, RTB_ERR_ARG, "rtb_set_option: unknown option or value");
 }

@@ -27,7 +27,8 @@ struct FanBuffers { // device pointers of one batched launch
 };
 
 // Launch the integrator on prepared device buffers (FINAL mode + exit points), no staging, no sync.
-int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n, int64_t max_size, cudaStream_t st = nullptr)
+int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n, int64_t max_size, cudaStream_t st = nullptr,
+               bool count_steps = true)
 {
     rtb_params pp = *p;
     pp.max_size = max_size;
@@ -39,6 +40,7 @@ int launch_fan(rtb_ctx *ctx, const rtb_params *p, const FanBuffers &b, int64_t n
     a.d_ray = b.d_ray;
     a.exit_out = b.exit_out;
     a.nonfinite = nullptr;
+    if (!count_steps) a.total_steps = nullptr; // the refinement counts the steps of the probes its passes consume
     // small batches: rays spread over the warps of all SMs (pick_lane_shift), 32-thread blocks; large ones run on
     // the ray queue (candidates of different length share warps at the candidate boundaries and, in the refinement,
     // converged pairs take no steps at all: the warps compact)
@@ -98,54 +100,92 @@ __device__ __forceinline__ void golden_probes(double a, double b, double &c, dou
     d = __dadd_rn(a, __dmul_rn(__dsub_rn(b, a), RTB_GOLD_RATIO));
 }
 
-// Pairs [i0, i0 + n) of the (C, Tn) problem; `f` holds this group's 2n probe rays.  active[0] counts the pairs that
+// Probe rays of one pair in a group's fan: P = 2 (c, d of the current bracket) or, when the passes are speculated two at
+// a time, P = 6: c, d, then the probes of the NEXT pass for both outcomes of this one -- c1, d1 of [a, d] (b = d, "left")
+// and of [c, b] (a = c).  Ray j of pair i sits at j*n + i.  Both outcomes are traced before either is known, so one
+// launch carries two passes of golden's loop (RT:188-194); the probes are formed by the same expressions the
+// one-pass-per-launch form uses after its decision, hence the same bits.
+__device__ __forceinline__ void write_probes(const FanBuffers &f, int64_t n, int64_t i, int P, double a, double b, int64_t M,
+                                             bool &active)
+{
+    double c, d;
+    golden_probes(a, b, c, d);
+    active = fabs(c - d) > RTB_GOLD_TOL;           // while abs(c - d) > tol
+    f.theta[i] = c; f.theta[n + i] = d;
+    const int64_t m0 = active ? M : 1;             // converged pairs stop tracing (max_size 1 = no step)
+    f.max_sizes[i] = m0; f.max_sizes[n + i] = m0;
+    if (P == 6) {
+        double cl, dl, cr, dr;
+        golden_probes(a, d, cl, dl);               // after b = d
+        golden_probes(c, b, cr, dr);               // after a = c
+        f.theta[2 * n + i] = cl; f.theta[3 * n + i] = dl; f.theta[4 * n + i] = cr; f.theta[5 * n + i] = dr;
+        const int64_t ml = (active && fabs(cl - dl) > RTB_GOLD_TOL) ? M : 1, mr = (active && fabs(cr - dr) > RTB_GOLD_TOL) ? M : 1;
+        f.max_sizes[2 * n + i] = ml; f.max_sizes[3 * n + i] = ml; f.max_sizes[4 * n + i] = mr; f.max_sizes[5 * n + i] = mr;
+    }
+}
+
+// Pairs [i0, i0 + n) of the (C, Tn) problem; `f` holds this group's P*n probe rays.  active[0] counts the pairs that
 // still iterate, active[1] takes the widest |c - d| of the group (positive doubles order like their bit patterns).
 __global__ void refine_init_kernel(const double *lo, const double *hi, const double *steps, const int64_t *max_sizes,
-                                   int64_t Tn, int64_t i0, int64_t n, double sx, double sy, double *a, double *b, FanBuffers f,
-                                   unsigned long long *active)
+                                   int64_t Tn, int64_t i0, int64_t n, int P, double sx, double sy, double *a, double *b,
+                                   FanBuffers f, unsigned long long *active)
 {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int64_t c = (i0 + i) / Tn;
     lo += i0; hi += i0; a += i0; b += i0;
     a[i] = lo[i]; b[i] = hi[i];
-    double pc, pd;
-    golden_probes(lo[i], hi[i], pc, pd);
-    const bool act = fabs(pc - pd) > RTB_GOLD_TOL;
-    f.theta[i] = pc; f.theta[n + i] = pd;
-    f.x0[i] = sx; f.x0[n + i] = sx; f.y0[i] = sy; f.y0[n + i] = sy;
-    f.steps[i] = steps[c]; f.steps[n + i] = steps[c];
-    const int64_t m = act ? max_sizes[c] : 1; // converged pairs stop tracing (max_size 1 = no step)
-    f.max_sizes[i] = m; f.max_sizes[n + i] = m;
+    for (int j = 0; j < P; ++j) { f.x0[j * n + i] = sx; f.y0[j * n + i] = sy; f.steps[j * n + i] = steps[c]; }
+    bool act;
+    write_probes(f, n, i, P, lo[i], hi[i], max_sizes[c], act);
     if (act) {
         atomicAdd(active, 1ull);
-        atomicMax(active + 1, (unsigned long long)__double_as_longlong(fabs(pc - pd)));
+        atomicMax(active + 1, (unsigned long long)__double_as_longlong(fabs(f.theta[i] - f.theta[n + i])));
     }
 }
 
-__global__ void refine_update_kernel(const double *tx, const double *ty, int64_t Tn, int64_t i0, int64_t n, double *a,
-                                     double *b, FanBuffers f, unsigned long long *active)
+// squared miss distance of probe ray j of pair i (un-fused multiply/add: numpy's value)
+__device__ __forceinline__ double miss2_of(const FanBuffers &f, int64_t n, int P, int j, int64_t i, double px, double py)
+{
+    const double dx = f.exit_out[j * n + i] - px, dy = f.exit_out[(int64_t)P * n + j * n + i] - py; // exit_out is (3, P n)
+    return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+}
+
+// One launch's worth of golden passes for every pair of the group: RT:188-194 once (P = 2) or twice (P = 6).
+// `useful` gets the ray-steps of the probes the passes actually consumed (the speculated branch not taken is work done,
+// not work counted).
+__global__ void refine_update_kernel(const double *tx, const double *ty, const int64_t *max_sizes, int64_t Tn, int64_t i0,
+                                     int64_t n, int P, double *a, double *b, FanBuffers f, unsigned long long *active,
+                                     unsigned long long *useful)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const double pc = f.theta[i], pd = f.theta[n + i];
-    if (!(fabs(pc - pd) > RTB_GOLD_TOL)) return; // while abs(c - d) > tol
-    const int64_t t = (i0 + i) % Tn;
-    a += i0; b += i0;
-    const double px = tx[t], py = ty[t];
-    const double *ex = f.exit_out, *ey = f.exit_out + 2 * n; // this launch had 2n rays: exit_out is (3, 2n)
-    double dx = ex[i] - px, dy = ey[i] - py;
-    const double fc = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    dx = ex[n + i] - px; dy = ey[n + i] - py;
-    const double fd = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    double va = a[i], vb = b[i];
-    if (fc < fd) vb = pd; else va = pc;
-    a[i] = va; b[i] = vb;
-    double nc, nd;
-    golden_probes(va, vb, nc, nd);
-    f.theta[i] = nc; f.theta[n + i] = nd;
-    if (fabs(nc - nd) > RTB_GOLD_TOL) atomicAdd(active, 1ull);
-    else { f.max_sizes[i] = 1; f.max_sizes[n + i] = 1; }
+    unsigned long long used = 0;
+    if (i < n) {
+        const double pc = f.theta[i], pd = f.theta[n + i];
+        if (fabs(pc - pd) > RTB_GOLD_TOL) { // while abs(c - d) > tol
+            const int64_t t = (i0 + i) % Tn;
+            const double px = tx[t], py = ty[t];
+            double va = a[i0 + i], vb = b[i0 + i];
+            const double *steps_of = f.d_ray + 2 * (int64_t)P * n; // d_ray is (3, P n): row 2 = steps taken
+            const bool left = miss2_of(f, n, P, 0, i, px, py) < miss2_of(f, n, P, 1, i, px, py); // if func(c) < func(d)
+            if (left) vb = pd; else va = pc;
+            used += (unsigned long long)(steps_of[i] + steps_of[n + i]);
+            if (P == 6) {
+                const int j = left ? 2 : 4;
+                const double c1 = f.theta[j * n + i], d1 = f.theta[(j + 1) * n + i];
+                if (fabs(c1 - d1) > RTB_GOLD_TOL) {
+                    if (miss2_of(f, n, P, j, i, px, py) < miss2_of(f, n, P, j + 1, i, px, py)) vb = d1; else va = c1;
+                    used += (unsigned long long)(steps_of[j * n + i] + steps_of[(j + 1) * n + i]);
+                }
+            }
+            a[i0 + i] = va; b[i0 + i] = vb;
+            bool act;
+            write_probes(f, n, i, P, va, vb, max_sizes[(i0 + i) / Tn], act);
+            if (act) atomicAdd(active, 1ull);
+        }
+    }
+    used = __reduce_add_sync(0xffffffffu, (unsigned)used) + 0ull; // < 2^32 per warp: 32 lanes x 4 rays x max_size < 2^31
+    if ((threadIdx.x & 31) == 0 && used) atomicAdd(useful, used);
 }
 
 __global__ void refine_final_fill_kernel(const double *a, const double *b, const double *steps, const int64_t *max_sizes,
@@ -310,13 +350,19 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
     for (int g = 0; g + 1 < G; ++g) if (!ctx->shoot_st[g]) CK(cudaStreamCreateWithFlags(&ctx->shoot_st[g], cudaStreamNonBlocking));
     for (int g = 0; g < G; ++g) if (!ctx->shoot_ev[g]) CK(cudaEventCreateWithFlags(&ctx->shoot_ev[g], cudaEventDisableTiming));
     unsigned long long *d_active = (unsigned long long *)sg.alloc(sizeof(unsigned long long) * 2 * G);
+    // Two passes per launch (6 probe rays per pair instead of 2, see write_probes): 1.5x the ray-steps for half the
+    // launches, for problems whose passes are bound by their longest ray rather than by throughput.  Opt-in
+    // (RTB_OPT_SHOOT_SPECULATE 2): measured slower on the configs[4] problem at every size tried -- even one GPU's share
+    // of it at N=8 (200 candidates x 512 targets) is throughput-bound: 32.7 ms against 48.2 ms speculated.
+    const bool spec = ctx->shoot_spec == 2;
+    const int P = spec ? 6 : 2;
     struct Group { int64_t i0, n; FanBuffers fb; cudaStream_t st; int iters; };
     std::vector<Group> gr(G);
     bool ok = sg.err == cudaSuccess && d_a && d_b && d_active;
     for (int g = 0; g < G && ok; ++g) {
         gr[g].i0 = n * g / G;
         gr[g].n = n * (g + 1) / G - gr[g].i0;
-        gr[g].fb = alloc_fan(sg, 2 * gr[g].n);
+        gr[g].fb = alloc_fan(sg, P * gr[g].n);
         gr[g].st = g == 0 ? st : ctx->shoot_st[g - 1];
         gr[g].iters = 0;
         ok = sg.err == cudaSuccess && gr[g].fb.exit_out;
@@ -333,7 +379,7 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
     int64_t launches = 0;
     for (int g = 0; g < G; ++g) {
         const Group &k = gr[g];
-        refine_init_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, st>>>(d_lo, d_hi, d_steps, d_msz, Tn, k.i0, k.n, q->src_x,
+        refine_init_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, st>>>(d_lo, d_hi, d_steps, d_msz, Tn, k.i0, k.n, P, q->src_x,
                                                                        q->src_y, d_a, d_b, k.fb, d_active + 2 * g);
         ++launches;
     }
@@ -349,7 +395,7 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
         // last pass of a pair by one (a pair that has converged takes no steps, so the spare pass costs nothing)
         int k = 0;
         while (w > RTB_GOLD_TOL && k < 4096) { w *= RTB_GOLD_RATIO; ++k; }
-        gr[g].iters = k + 1;
+        gr[g].iters = spec ? (k + 2) / 2 : k + 1; // launches: two passes each when speculating
         iters = std::max<int64_t>(iters, k);
     }
     // fork: the side streams start after the brackets are initialised
@@ -364,9 +410,10 @@ extern "C" int rtb_shoot_refine(rtb_ctx *ctx, const rtb_params *p, const rtb_sho
         for (int g = 0; g < G; ++g) {
             const Group &k = gr[g];
             if (it >= k.iters) continue;
-            if ((rc = launch_fan(ctx, p, k.fb, 2 * k.n, M, k.st))) return bail(rc);
-            refine_update_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, k.st>>>(d_tx, d_ty, Tn, k.i0, k.n, d_a, d_b, k.fb,
-                                                                               d_active + 2 * g + (it == k.iters - 1 ? 0 : 1)); // [2g]: pairs left after the last pass; [2g+1]: sink
+            if ((rc = launch_fan(ctx, p, k.fb, P * k.n, M, k.st, false))) return bail(rc);
+            refine_update_kernel<<<(unsigned)((k.n + 255) / 256), 256, 0, k.st>>>(d_tx, d_ty, d_msz, Tn, k.i0, k.n, P, d_a, d_b, k.fb,
+                                                                               d_active + 2 * g + (it == k.iters - 1 ? 0 : 1), // [2g]: pairs left after the last pass; [2g+1]: sink
+                                                                               ctx->d_total);
             launches += 2;
         }
     }

@@ -223,9 +223,9 @@ class Engine:
 
     def set_option(self, name, value):
         """Tuning / test switches (include/rtb.h rtb_set_option): "queue" 0 auto | 1 always | 2 never (static grid);
-        "traj_store" 0 per-lane stores (default) | 1 rows staged in shared memory + TMA stores; "shoot_groups" 0 auto | 1..16."""
+        "traj_store" 0 per-lane stores (default) | 1 rows staged in shared memory + TMA stores; "shoot_groups" 0 auto | 1..16; "shoot_speculate" 0 | 1 off (default) | 2 on."""
         opt = {"queue": _cabi.RTB_OPT_QUEUE, "traj_store": _cabi.RTB_OPT_TRAJ_STORE,
-               "shoot_groups": _cabi.RTB_OPT_SHOOT_GROUPS}[name]
+               "shoot_groups": _cabi.RTB_OPT_SHOOT_GROUPS, "shoot_speculate": _cabi.RTB_OPT_SHOOT_SPECULATE}[name]
         self._check(self._lib.rtb_set_option(self._ctx, opt, int(value)))
 
     def build_id(self):

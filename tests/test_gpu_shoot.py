@@ -118,3 +118,33 @@ def test_shoot_edge_cases(engine):
     assert rf.iterations == 0 and rf.theta[0, 0] == (hi[0, 0] + lo[0, 0]) / 2 and rf.result[4, 0, 0] > 10
     with pytest.raises(_cabi.RtbError):
         engine.shoot_coarse(6, ang, (-2.0, -2.0), [step], [0], (np.array([0.0]), np.array([1.0])), gamma, box)
+
+
+@pytest.mark.parametrize("uc,m,n_t", [("1", 6, 700), ("3", 8, 37)])
+def test_speculated_passes_give_the_same_search(engine, uc, m, n_t):
+    """rtb_shoot_refine with two golden passes per launch (both outcomes of a pass traced before it is decided,
+    RTB_OPT_SHOOT_SPECULATE 2) == one pass per launch, bit for bit: theta, results, pass count; and fewer launches.
+    The counted ray-steps are those of the probes the passes consumed, the same either way."""
+    z, grd, gamma, box = _setup(uc)
+    engine.set_field(z, grd)
+    steps = np.array([rt.SIGMA / 3.0, rt.SIGMA / 1.3, rt.SIGMA / 2.0])
+    msz = rt.candidate_rows(uc, steps)
+    lo_a = 2 * np.pi / 60 if uc == "1" else 0.0
+    angles = np.linspace(lo_a, np.pi / 2, 257)
+    true = np.linspace(0.25, 1.5, n_t) + 1.7e-4
+    tx, ty, _ = rt.targets_from_angles(engine, m, uc, true, steps[0])
+    co = engine.shoot_coarse(m, angles, (-2.0, -2.0), steps, msz, (tx, ty), gamma, box)
+    lo, hi = rt.brackets_from_index(co.index, angles)
+    lo[1, ::5] = hi[1, ::5] - 1e-9                      # some pairs converged from the start, some brackets narrower
+    hi[2, 1::3] = lo[2, 1::3] + 0.37 * (hi[2, 1::3] - lo[2, 1::3])
+    out = []
+    try:
+        for mode in (1, 2):
+            engine.set_option("shoot_speculate", mode)
+            out.append(engine.shoot_refine(m, lo, hi, (-2.0, -2.0), steps, msz, (tx, ty), gamma, box))
+    finally:
+        engine.set_option("shoot_speculate", 0)
+    a, b = out
+    assert np.array_equal(a.theta, b.theta) and np.array_equal(a.result, b.result, equal_nan=True)
+    assert a.iterations == b.iterations and a.stats["ray_steps"] == b.stats["ray_steps"]
+    assert b.stats["launches"] < a.stats["launches"]
