@@ -733,6 +733,8 @@ def run_secondary_configs(ctx):
                      ("aniso_16M_op11", lambda: run_trace_config(ctx, "aniso_16M_op11", "4", 24, 11, "op11_stats_aniso")),
                      ("aniso_16M_op10", lambda: run_trace_config(ctx, "aniso_16M_op10", "4", 24, 10, "op10_stats_aniso")),
                      ("shoot_4096x4096x200", lambda: run_shoot_config(ctx))):
+        if ctx["args"].only and name not in ctx["args"].only.split(","):
+            continue
         t0 = time.perf_counter()
         e = fn()
         if e is not None:
@@ -749,6 +751,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--configs", default="all", choices=["all", "headline"],
                     help="all = the headline + BASELINE configs[0], [2], [3], [4] in the `configs` object (default)")
+    ap.add_argument("--only", default="", help="comma-separated names of the `configs` entries to run (default: all of them)")
     ap.add_argument("--no-full", action="store_true", help="skip the FULL-trajectory (45.8 GB s_ray) legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],

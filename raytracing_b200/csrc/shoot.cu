@@ -102,25 +102,32 @@ __device__ __forceinline__ void golden_probes(double a, double b, double &c, dou
 
 // Probe rays of one pair in a group's fan: P = 2 (c, d of the current bracket) or, when the passes are speculated two at
 // a time, P = 6: c, d, then the probes of the NEXT pass for both outcomes of this one -- c1, d1 of [a, d] (b = d, "left")
-// and of [c, b] (a = c).  Ray j of pair i sits at j*n + i.  Both outcomes are traced before either is known, so one
+// and of [c, b] (a = c).  Ray j of pair i sits at slot i*P + j (probe_slot).  Both outcomes are traced before either is known, so one
 // launch carries two passes of golden's loop (RT:188-194); the probes are formed by the same expressions the
 // one-pass-per-launch form uses after its decision, hence the same bits.
+//
+// Slot order: the probes of one pair are neighbours in the fan.  c and d are 0.24 of the bracket apart and the bracket
+// shrinks by 0.618 per pass, so from the third pass on a warp covers the launch angles of 16 targets instead of 32 and
+// its lanes sit in about half as many field cells -- the refinement is bound by the L1 data pipe (one wavefront per
+// distinct cell record per load, profiles/r2_ncu_shoot_refine.csv), not by FP64.
+__device__ __forceinline__ int64_t probe_slot(int P, int j, int64_t i) { return i * P + j; }
+
 __device__ __forceinline__ void write_probes(const FanBuffers &f, int64_t n, int64_t i, int P, double a, double b, int64_t M,
                                              bool &active)
 {
     double c, d;
     golden_probes(a, b, c, d);
     active = fabs(c - d) > RTB_GOLD_TOL;           // while abs(c - d) > tol
-    f.theta[i] = c; f.theta[n + i] = d;
+    f.theta[probe_slot(P, 0, i)] = c; f.theta[probe_slot(P, 1, i)] = d;
     const int64_t m0 = active ? M : 1;             // converged pairs stop tracing (max_size 1 = no step)
-    f.max_sizes[i] = m0; f.max_sizes[n + i] = m0;
+    f.max_sizes[probe_slot(P, 0, i)] = m0; f.max_sizes[probe_slot(P, 1, i)] = m0;
     if (P == 6) {
         double cl, dl, cr, dr;
         golden_probes(a, d, cl, dl);               // after b = d
         golden_probes(c, b, cr, dr);               // after a = c
-        f.theta[2 * n + i] = cl; f.theta[3 * n + i] = dl; f.theta[4 * n + i] = cr; f.theta[5 * n + i] = dr;
+        f.theta[i * 6 + 2] = cl; f.theta[i * 6 + 3] = dl; f.theta[i * 6 + 4] = cr; f.theta[i * 6 + 5] = dr;
         const int64_t ml = (active && fabs(cl - dl) > RTB_GOLD_TOL) ? M : 1, mr = (active && fabs(cr - dr) > RTB_GOLD_TOL) ? M : 1;
-        f.max_sizes[2 * n + i] = ml; f.max_sizes[3 * n + i] = ml; f.max_sizes[4 * n + i] = mr; f.max_sizes[5 * n + i] = mr;
+        f.max_sizes[i * 6 + 2] = ml; f.max_sizes[i * 6 + 3] = ml; f.max_sizes[i * 6 + 4] = mr; f.max_sizes[i * 6 + 5] = mr;
     }
 }
 
@@ -135,19 +142,20 @@ __global__ void refine_init_kernel(const double *lo, const double *hi, const dou
     const int64_t c = (i0 + i) / Tn;
     lo += i0; hi += i0; a += i0; b += i0;
     a[i] = lo[i]; b[i] = hi[i];
-    for (int j = 0; j < P; ++j) { f.x0[j * n + i] = sx; f.y0[j * n + i] = sy; f.steps[j * n + i] = steps[c]; }
+    for (int j = 0; j < P; ++j) { f.x0[i * P + j] = sx; f.y0[i * P + j] = sy; f.steps[i * P + j] = steps[c]; }
     bool act;
     write_probes(f, n, i, P, lo[i], hi[i], max_sizes[c], act);
     if (act) {
         atomicAdd(active, 1ull);
-        atomicMax(active + 1, (unsigned long long)__double_as_longlong(fabs(f.theta[i] - f.theta[n + i])));
+        atomicMax(active + 1, (unsigned long long)__double_as_longlong(fabs(f.theta[probe_slot(P, 0, i)] - f.theta[probe_slot(P, 1, i)])));
     }
 }
 
 // squared miss distance of probe ray j of pair i (un-fused multiply/add: numpy's value)
 __device__ __forceinline__ double miss2_of(const FanBuffers &f, int64_t n, int P, int j, int64_t i, double px, double py)
 {
-    const double dx = f.exit_out[j * n + i] - px, dy = f.exit_out[(int64_t)P * n + j * n + i] - py; // exit_out is (3, P n)
+    const int64_t k = probe_slot(P, j, i);
+    const double dx = f.exit_out[k] - px, dy = f.exit_out[(int64_t)P * n + k] - py; // exit_out is (3, P n)
     return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
 }
 
@@ -161,7 +169,7 @@ __global__ void refine_update_kernel(const double *tx, const double *ty, const i
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long used = 0;
     if (i < n) {
-        const double pc = f.theta[i], pd = f.theta[n + i];
+        const double pc = f.theta[probe_slot(P, 0, i)], pd = f.theta[probe_slot(P, 1, i)];
         if (fabs(pc - pd) > RTB_GOLD_TOL) { // while abs(c - d) > tol
             const int64_t t = (i0 + i) % Tn;
             const double px = tx[t], py = ty[t];
@@ -169,13 +177,13 @@ __global__ void refine_update_kernel(const double *tx, const double *ty, const i
             const double *steps_of = f.d_ray + 2 * (int64_t)P * n; // d_ray is (3, P n): row 2 = steps taken
             const bool left = miss2_of(f, n, P, 0, i, px, py) < miss2_of(f, n, P, 1, i, px, py); // if func(c) < func(d)
             if (left) vb = pd; else va = pc;
-            used += (unsigned long long)(steps_of[i] + steps_of[n + i]);
+            used += (unsigned long long)(steps_of[probe_slot(P, 0, i)] + steps_of[probe_slot(P, 1, i)]);
             if (P == 6) {
                 const int j = left ? 2 : 4;
-                const double c1 = f.theta[j * n + i], d1 = f.theta[(j + 1) * n + i];
+                const double c1 = f.theta[probe_slot(P, j, i)], d1 = f.theta[probe_slot(P, j + 1, i)];
                 if (fabs(c1 - d1) > RTB_GOLD_TOL) {
                     if (miss2_of(f, n, P, j, i, px, py) < miss2_of(f, n, P, j + 1, i, px, py)) vb = d1; else va = c1;
-                    used += (unsigned long long)(steps_of[j * n + i] + steps_of[(j + 1) * n + i]);
+                    used += (unsigned long long)(steps_of[probe_slot(P, j, i)] + steps_of[probe_slot(P, j + 1, i)]);
                 }
             }
             a[i0 + i] = va; b[i0 + i] = vb;

@@ -122,22 +122,27 @@ def shooting_search(option, z, grd, user_choice, targets, angles, steps=None, di
         dev = getattr(eng, "torch_device", None) or torch.device("cuda", eng.device)
         to = lambda a: torch.as_tensor(a).to(dev)
         d_steps, d_msz, d_tx, d_ty = to(steps), to(msz), to(tx), to(ty)
-        # Coarse fan sharded by angle, refinement by target -- both dealt round-robin (rank r takes angles / targets
-        # r, r + world, ...): rays near the critical angle run to max_size, and contiguous shards would hand all of
-        # them to one rank (measured at N=8: the slowest rank took 48 ms of kernels against 22 ms on average).
-        ang_l = angles[rank::world]
-        if ang_l.size:
-            co = eng.shoot_coarse(option, to(np.ascontiguousarray(ang_l)), src, d_steps, d_msz, (d_tx, d_ty), gamma, box,
+        # Coarse fan sharded by angle, refinement by target -- both dealt block-cyclically in blocks of 64 (two warps of
+        # neighbours).  Rays near the critical angle run to max_size, so contiguous shards hand one rank most of the
+        # work (measured at N=8: 48 ms of kernels on the slowest rank against 22 ms on average); dealing single angles
+        # round-robin balances the ranks but puts rays 8 launch-angle steps apart into neighbouring lanes, which costs
+        # more in field-cell locality than the balance gains (55 ms).  Blocks keep a warp's rays adjacent.
+        from .dist import cyclic_indices
+        BLK = 64
+        aidx = cyclic_indices(A, world, rank, BLK)
+        if aidx.size:
+            co = eng.shoot_coarse(option, to(np.ascontiguousarray(angles[aidx])), src, d_steps, d_msz, (d_tx, d_ty), gamma, box,
                                   exact=exact)
             add(co.stats)
-            miss2, index = co.miss2, co.index * world + rank    # local position -> index into `angles`
+            miss2, index = co.miss2, to(aidx)[co.index]     # local position -> index into `angles`
         else:
             miss2 = torch.full((Cn, Tn), float("inf"), dtype=torch.float64, device=dev)
             index = torch.full((Cn, Tn), INT64_MAX, dtype=torch.int64, device=dev)
         miss2, index = reduce_argmin(miss2, index, grp)   # the path's real exchange step (NCCL MIN)
-        mine = torch.arange(rank, Tn, world, device=dev)
+        owners = [cyclic_indices(Tn, world, r, BLK) for r in range(world)]
+        mine = to(owners[rank])
         lo, hi = brackets_from_index(index[:, mine].contiguous(), to(angles))
-        Tl = (Tn + world - 1) // world                     # targets per rank, padded to the same length for the gather
+        Tl = max(o.size for o in owners)                   # targets per rank, padded to the same length for the gather
         part = torch.zeros(6, Cn, Tl, dtype=torch.float64, device=dev)
         iters = 0
         if mine.numel():
@@ -148,8 +153,9 @@ def shooting_search(option, z, grd, user_choice, targets, angles, steps=None, di
             iters = rf.iterations
         bufs = [torch.empty_like(part) for _ in range(world)]
         dist.all_gather(bufs, part, group=grp)             # result gather
-        # target t sits in slot t // world of rank t % world
-        full = torch.stack(bufs, dim=3).reshape(6, Cn, Tl * world)[:, :, :Tn].contiguous()
+        full = torch.empty(6, Cn, Tn, dtype=torch.float64, device=dev)
+        for r in range(world):
+            full[:, :, to(owners[r])] = bufs[r][:, :, :owners[r].size]
         it = torch.tensor([iters], dtype=torch.int64, device=dev)
         dist.all_reduce(it, op=dist.ReduceOp.MAX, group=grp)
         iters = int(it.item())
