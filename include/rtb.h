@@ -206,6 +206,25 @@ int rtb_sweep(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const dou
               const rtb_sweep_spec *spec, double *sum, double *max, int64_t *count, rtb_stats *stats);
 
 /*
+ * rtb_sweep for callers that cannot allocate.  No counterpart in the reference: added
+ * (code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc).
+ *
+ * Same kernels, arguments and results as rtb_sweep, but the per-ray scratch (d_ray, last rows / p_x statistics of all
+ * C * R rays) lives in one file-scope array in device memory -- RTB_NOALLOC_MAX_RAYS rays x 9 doubles = 9 MiB held by
+ * every GPU that loads the library until the process exits -- and the call makes no cudaMalloc / cudaFree or any other
+ * allocating call.  Limits, each rejected with RTB_ERR_ARG and a message in rtb_last_error:
+ *   - p->ptr_kind must be RTB_PTR_DEVICE (theta0, x0, y0, spec->steps, spec->max_sizes, sum, max, count on the device);
+ *   - spec->metric RTB_SWEEP_CLOSURE or RTB_SWEEP_PX_CV (the Snell metric needs checkpoint buffers sized by the call);
+ *   - spec->C <= RTB_NOALLOC_MAX_CANDIDATES and spec->C * R <= RTB_NOALLOC_MAX_RAYS.
+ * All calls on one GPU share the array: calls that overlap on the GPU (two contexts / streams) race.  The array keeps
+ * the previous call's contents; the part a call uses is cleared at its start.
+ */
+#define RTB_NOALLOC_MAX_RAYS 131072
+#define RTB_NOALLOC_MAX_CANDIDATES 256
+int rtb_sweep_noalloc(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0, const double *y0,
+                      int64_t R, const rtb_sweep_spec *spec, double *sum, double *max, int64_t *count, rtb_stats *stats);
+
+/*
  * Batched two-point shooting search (BASELINE.json configs[4]).  The reference has NO two-point
  * search -- README.md:6 "shooting method" is the forward fan of trazar, and scipy.optimize.minimize
  * is imported (RT:48) but never called -- so these two calls are defined from reference parts

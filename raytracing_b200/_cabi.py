@@ -18,7 +18,7 @@ EXPORTS = ("rtb_create", "rtb_destroy", "rtb_set_stream", "rtb_last_error", "rtb
            "rtb_set_field", "rtb_field_eval", "rtb_trace", "rtb_fp64_peak", "rtb_shoot_coarse", "rtb_shoot_refine", "rtb_wavefront",
            "rtb_fit_field", "rtb_gradient", "rtb_get_field",
            "rtb_gather_alloc", "rtb_gather_open", "rtb_gather_close", "rtb_set_gather", "rtb_set_gather_cyclic",
-           "rtb_sweep", "rtb_set_option", "rtb_build_id", "rtb_kernel_id")
+           "rtb_sweep", "rtb_sweep_noalloc", "rtb_set_option", "rtb_build_id", "rtb_kernel_id")
 
 
 class RtbSpline(C.Structure):
@@ -113,6 +113,8 @@ def load():
     lib.rtb_sweep.restype = C.c_int
     lib.rtb_sweep.argtypes = [vp, C.POINTER(RtbParams), vp, vp, vp, i64, C.POINTER(RtbSweepSpec), vp, vp, vp,
                               C.POINTER(RtbStats)]
+    lib.rtb_sweep_noalloc.restype = C.c_int
+    lib.rtb_sweep_noalloc.argtypes = lib.rtb_sweep.argtypes
     lib.rtb_set_option.restype = C.c_int
     lib.rtb_set_option.argtypes = [vp, i32, i32]
     lib.rtb_build_id.restype = C.c_char_p

@@ -8,6 +8,8 @@
 // r / R (TraceArgs.cand_R).  Candidates are processed in groups of at most 2^26 rays.
 #include "ctx.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int RED_T = 256;
@@ -156,6 +158,116 @@ extern "C" int rtb_sweep(rtb_ctx *ctx, const rtb_params *p, const double *theta0
         stats->nonfinite_rays = (int64_t)counters[1];
         stats->launches = launches;
         stats->h2d_bytes = sg.h2d; stats->d2h_bytes = sg.d2h;
+    }
+    return RTB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// rtb_sweep_noalloc: the same sweep for callers that must not allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+//
+// rtb_sweep parks the per-ray results of the trace kernel (d_ray, last rows / p_x statistics) in pool buffers obtained
+// with cudaMalloc and hands them to sweep_reduce_kernel; here the same kernels use one fixed array in device memory
+// instead: RTB_NOALLOC_MAX_RAYS rays x 9 doubles = 9 MiB, resident on every GPU that loads the library until the
+// process exits.  Every call on a device shares it (calls that overlap on the GPU race), and it keeps the previous
+// call's contents, so the part a call uses is cleared first.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_sweep_scratch[(size_t)RTB_NOALLOC_MAX_RAYS * 9];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double *g_sweep_scratch_addr[NOALLOC_MAX_DEVICES]; // device address of g_sweep_scratch per device (host code may not
+std::mutex g_sweep_scratch_mutex;                  // pass the symbol itself: its name is a host-side stand-in)
+} // namespace
+
+extern "C" int rtb_sweep_noalloc(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0,
+                                 const double *y0, int64_t R, const rtb_sweep_spec *spec, double *sum, double *mx,
+                                 int64_t *count, rtb_stats *stats)
+{
+    if (!ctx) return RTB_ERR_ARG;
+    if (!ctx->has_field) return fail(ctx, RTB_ERR_NOFIELD, "rtb_sweep_noalloc: no field set (rtb_set_field)");
+    if (!p || !spec || !theta0 || !x0 || !y0 || !sum || !mx || !count || !spec->steps || !spec->max_sizes)
+        return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: null argument");
+    if (p->ptr_kind != RTB_PTR_DEVICE)
+        return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: device pointers only (RTB_PTR_DEVICE): host arrays would need staging buffers");
+    if (p->method < 1 || p->method > 11) return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: method must be 1..11");
+    if (spec->metric != RTB_SWEEP_CLOSURE && spec->metric != RTB_SWEEP_PX_CV)
+        return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: metric must be RTB_SWEEP_CLOSURE or RTB_SWEEP_PX_CV (the Snell metric "
+                                      "re-integrates from checkpoint buffers sized by the call: use rtb_sweep)");
+    if (R < 0 || spec->C < 0 || spec->skip_lo < 0 || spec->skip_hi < 0) return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: negative size");
+    const int64_t C = spec->C;
+    if (C > RTB_NOALLOC_MAX_CANDIDATES)
+        return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: more than RTB_NOALLOC_MAX_CANDIDATES (256) candidates");
+    if (R > RTB_NOALLOC_MAX_RAYS || C * R > RTB_NOALLOC_MAX_RAYS)
+        return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: C * R exceeds RTB_NOALLOC_MAX_RAYS (131072 rays in all): split the "
+                                      "candidates over several calls or use rtb_sweep");
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES) return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: device index");
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    if (C == 0) return RTB_OK;
+    CK(cudaSetDevice(ctx->device));
+    double *scratch;
+    { // once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_sweep_scratch_mutex);
+        if (!g_sweep_scratch_addr[ctx->device]) {
+            double *ptr = nullptr;
+            CK(cudaGetSymbolAddress((void **)&ptr, g_sweep_scratch));
+            g_sweep_scratch_addr[ctx->device] = ptr;
+        }
+        scratch = g_sweep_scratch_addr[ctx->device];
+    }
+    cudaStream_t st = ctx->stream;
+    const int metric = spec->metric;
+
+    // warp-uniform loop bound of the kernel = the largest candidate (read back into a fixed host array)
+    int64_t hm[RTB_NOALLOC_MAX_CANDIDATES];
+    CK(cudaMemcpyAsync(hm, spec->max_sizes, sizeof(int64_t) * C, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    int64_t Mmax = 1;
+    for (int64_t c = 0; c < C; ++c) {
+        if (hm[c] < 1 || hm[c] > 0x7fffffff) return fail(ctx, RTB_ERR_ARG, "rtb_sweep_noalloc: bad max_sizes entry");
+        Mmax = std::max(Mmax, hm[c]);
+    }
+
+    const int64_t n = C * R;
+    CK(cudaEventRecord(ctx->ev[0], st));
+    CK(cudaMemsetAsync(ctx->d_total, 0, 2 * sizeof(unsigned long long), st));
+    // the array keeps the last call's contents: rows a ray does not reach must read as zeros (np.zeros RT:802)
+    if (n > 0) CK(cudaMemsetAsync(scratch, 0, sizeof(double) * 9 * n, st));
+    double *d_ray = scratch, *d_last = nullptr, *d_px = nullptr; // (3, n) | (6, n) or (3, n)
+    if (metric == RTB_SWEEP_CLOSURE) d_last = scratch + 3 * n;
+    else d_px = scratch + 3 * n;
+    rtb_params pp = *p;
+    pp.max_size = Mmax; pp.steps = nullptr; pp.max_sizes = nullptr; pp.step = 1.0;
+    int64_t launches = 0;
+    CK(cudaEventRecord(ctx->ev[1], st));
+    if (n > 0) {
+        TraceArgs a = rtb_base_args(ctx, &pp, 1);
+        a.theta0 = theta0; a.x0 = x0; a.y0 = y0;
+        a.steps = spec->steps; a.max_sizes = spec->max_sizes;
+        a.cand_R = R; a.R = n;
+        a.lane_shift = pick_lane_shift(n);
+        a.stage = n >= (1 << 16);
+        a.d_ray = d_ray; a.last_row = d_last; a.px_stats = d_px;
+        const int rc = rtb_launch(ctx, st, &pp, a, false);
+        if (rc) { cudaStreamSynchronize(st); return rc; }
+        ++launches;
+    }
+    sweep_reduce_kernel<<<(unsigned)C, RED_T, 0, st>>>(metric, R, spec->skip_lo, spec->skip_hi, nullptr, d_ray, d_last, d_px,
+                                                       spec->max_sizes, n, sum, mx, count);
+    CK(cudaGetLastError());
+    ++launches;
+    CK(cudaEventRecord(ctx->ev[2], st));
+    unsigned long long counters[2] = {0, 0};
+    CK(cudaMemcpyAsync(counters, ctx->d_total, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ctx->ev[3], st));
+    CK(cudaStreamSynchronize(st));
+    if (stats) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); stats->kernel_ms = ms;
+        cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); stats->total_ms = ms;
+        stats->ray_steps = (int64_t)counters[0];
+        stats->nonfinite_rays = (int64_t)counters[1];
+        stats->launches = launches;
     }
     return RTB_OK;
 }

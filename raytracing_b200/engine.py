@@ -257,6 +257,29 @@ class Engine:
                                         C.byref(spec), sm.ctypes.data, mx.ctypes.data, cnt.ctypes.data, C.byref(stats)))
         return sm, mx, cnt, self._stats(stats)
 
+    def sweep_noalloc(self, method, theta0, x0, y0, steps, max_sizes, gamma, box, metric, sum, max, count,
+                      skip_lo=0, skip_hi=0, exact=False, ptr_kind=_cabi.RTB_PTR_DEVICE):
+        """rtb_sweep_noalloc: rtb_sweep on the library's fixed scratch array, for callers that cannot allocate (no
+        counterpart in the reference).  Every array is a contiguous torch CUDA tensor the CALLER made -- inputs and the
+        outputs sum / max (float64, C) and count (int64, C); nothing is allocated here or in the library.
+        metric: "closure" | "px_cv"; C * R <= RTB_NOALLOC_MAX_RAYS.  Returns stats."""
+        self.use_torch_stream()
+        R, Cn = theta0.numel(), steps.numel()
+        for t in (theta0, x0, y0, steps, max_sizes, sum, max, count):
+            assert t.is_cuda and t.is_contiguous()
+        assert x0.numel() == R and y0.numel() == R and max_sizes.numel() == Cn
+        assert sum.numel() == Cn and max.numel() == Cn and count.numel() == Cn
+        mid = {"snell": _cabi.RTB_SWEEP_SNELL, "closure": _cabi.RTB_SWEEP_CLOSURE, "px_cv": _cabi.RTB_SWEEP_PX_CV}[metric]
+        flags = _cabi.RTB_F_EXACT_BASIS if exact else 0
+        p = _cabi.RtbParams(method_id(method), flags, ptr_kind, 1, 1, float(gamma), 0.0,
+                            float(box[0]), float(box[1]), float(box[2]), float(box[3]), None, None)
+        spec = _cabi.RtbSweepSpec(steps.data_ptr(), max_sizes.data_ptr(), Cn, mid, int(skip_lo), int(skip_hi))
+        stats = _cabi.RtbStats()
+        self._check(self._lib.rtb_sweep_noalloc(self._ctx, C.byref(p), theta0.data_ptr(), x0.data_ptr(), y0.data_ptr(), R,
+                                                C.byref(spec), sum.data_ptr(), max.data_ptr(), count.data_ptr(),
+                                                C.byref(stats)))
+        return self._stats(stats)
+
     def fp64_peak(self):
         v = C.c_double()
         self._check(self._lib.rtb_fp64_peak(self._ctx, C.byref(v)))
