@@ -10,6 +10,8 @@
 // Every deviation from the faithful kernel is rounding-level (<= 1e-13 over a trajectory, see
 // tests/test_gpu_trace.py) except where the reference itself is noise-dominated.
 #pragma once
+#include <type_traits>
+
 #include "fastmath.cuh"
 #include "golden_table.cuh"
 #include "step.cuh"
@@ -211,21 +213,17 @@ static __device__ __noinline__ bool golden_trig_tie(const F cost, const TIE t, d
     }
 }
 
+// Passes [k, kend) of the evaluating search: a call-free inner loop (its state stays in registers); a pass inside the
+// band leaves it, is decided out of line, and the loop resumes behind it.
 template <class F, class TIE>
-__device__ __forceinline__ double golden_trig(const F &cost, const TIE &ref, double scale, double theta, double st,
-                                              double ct, double &s_out, double &c_out)
+__device__ __forceinline__ void golden_trig_passes(const F &cost, const TIE &ref, double tie2, double theta, double st,
+                                                   double ct, TrigState &g, int &k, int kend)
 {
-    const double tie2 = (RTB_TIE_EPS * scale) * (RTB_TIE_EPS * scale);
-    TrigState g;
-    trig_init(cost, st, ct, g);
-    // The passes run in a call-free inner loop (its state stays in registers); a pass inside the band leaves it, is
-    // decided out of line, and the loop resumes behind it.
-    int k = 0;
     for (;;) {
         bool band = false;
         double df;
 #pragma unroll 1
-        for (; k < RTB_GOLDEN_ITERS; ++k) {
+        for (; k < kend; ++k) {
             if (trig_in_band(g, tie2, df)) { band = true; break; }
             trig_advance(cost, g, trig_decide(g, df), k);
         }
@@ -234,6 +232,180 @@ __device__ __forceinline__ double golden_trig(const F &cost, const TIE &ref, dou
         trig_advance(cost, g, left ? RTB_SIGN : 0, k);
         ++k;
     }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Anisotropic cost, passes k >= RTB_GOLDEN_TAIL_K1 without cost evaluations.
+//
+// After K1 passes the bracket is pi rho^K1 wide (9.8e-3 for K1 = 12) and the cost f is, to the accuracy a decision
+// needs, its cubic Taylor polynomial about the minimiser x*: with e = (midpoint of the probes) - x*, q = half their
+// distance, kappa = f3/f2 and lambda = f4/f2 (fn = n-th derivative of f at x*),
+//     f(d) - f(c) = 2 q f2 [ e + kappa (e^2/2 + q^2/6) + O(lambda (|e| + q)^3) ],
+// so RT:189 `f(c) < f(d)` <=> t = e + kappa (e^2/2 + q^2/6) > 0.  x* comes from three or four Newton steps on the first
+// derivative started at the kept probe (first and second derivative in closed form from the residuals,
+// aniso_cost_d12), kappa from the secant of the second derivative over the first step.  A pass is decided by the sign
+// of t unless |t| is within a band that covers
+//   - the band of the evaluating search in the same units (|f(c) - f(d)| <= TIE sqrt(f(c) + f(d)): there the
+//     reference's own rounding decides), widened by a quarter,
+//   - the cubic's truncation error lambda_max (|e| + q)^3 / 3 with lambda_max = 16 max(gamma, 1/gamma)^2 + 8 (measured
+//     maximum 118 at gamma = 3: tools/proto/golden_tail.py), the error of the secant kappa, the last Newton step squared;
+// a pass inside the band is decided exactly as before, by golden_trig_tie (replay of the evaluating search next to the
+// reference's bracket).  Outside the band the decision equals the evaluating search's (prototype: 0 differences in
+// 2e5 random steps x 25 passes for gamma = 0.5, 1.5, 3), hence the reference's.  Steps where the expansion is not
+// trustworthy (second derivative <= 0, Newton not converged, x* outside the bracket, |kappa| > 64) return false and
+// take the evaluating passes.  5 FP64 instructions per pass instead of 19, straight-line; a step with a pass inside
+// the band repeats its tail in golden_aniso_tail_ties (rolled, with the out-of-line decisions).
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef RTB_GOLDEN_TAIL_K1
+#define RTB_GOLDEN_TAIL_K1 12
+#endif
+
+// F1 = half the first, F2 = half the second derivative, and the value f of the anisotropic cost at the angle with
+// (sin, cos) = (s, c).  With y = 1/sqrt(v), v = 1 + (gamma^2 - 1) s^2: (c y)' = -gamma^2 s y^3, (s y)' = c y^3,
+// (v y)' = (gamma^2 - 1) s c y.
+__device__ __forceinline__ void aniso_cost_d12(const CostAnisoFast &cf, double s, double c, double &F1, double &F2, double &f)
+{
+    const double v = fma(cf.g2m1, s * s, 1.0);
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
+    const double er = fma(-v * y, y, 1.0);
+    y = fma(y, fma(er, 0.375, 0.5) * er, y);
+    const double w = v * y;
+    const double Rx = fma(cf.n1, c * y, -fma(w, cf.gx1h, cf.mx));
+    const double Ry = fma(cf.n1g2, s * y, -fma(w, cf.gy1h, cf.my));
+    const double y2 = y * y, By3 = cf.n1g2 * (y2 * y), z = cf.g2m1 * (s * c), zy = z * y;
+    const double Rx1 = -fma(By3, s, zy * cf.gx1h);
+    const double Ry1 = fma(By3, c, -(zy * cf.gy1h));
+    F1 = fma(Rx, Rx1, Ry * Ry1);
+    const double z1 = cf.g2m1 * fma(c, c, -(s * s));
+    const double t1 = z * y2;
+    const double q2 = fma(z1, y, -(zy * t1));
+    const double u = 3.0 * By3 * t1;
+    const double Rx2 = fma(u, s, -fma(By3, c, q2 * cf.gx1h));
+    const double Ry2 = -fma(u, c, fma(By3, s, q2 * cf.gy1h));
+    F2 = __dadd_rn(fma(Rx1, Rx1, Ry1 * Ry1), fma(Rx, Rx2, Ry * Ry2));
+    f = fma(Rx, Rx, Ry * Ry);
+}
+
+// What the tail passes need besides the cost: the expansion and its bands.
+struct AnisoTail {
+    double kaph;   // kappa / 2
+    double apx;    // error bound of the expansion, x rho^(2k) in pass k
+    double na, nb; // band of the evaluating search in units of t: na / q + nb
+    double e0;     // midpoint of the probes of pass K1 minus x*
+};
+
+__device__ __forceinline__ bool aniso_tail_in_band(const AnisoTail &a, const GoldenTail &t, double e, double &tt)
+{
+    tt = fma(a.kaph, fma(e, e, 2.0 * t.q26), e);
+    const double bd = fma(a.apx, t.r2, fma(a.na, t.invq, a.nb));
+    return (__double2hiint(tt) & 0x7fffffff) <= __double2hiint(bd);
+}
+
+// RT:189: f(c) < f(d), i.e. t > 0: b = d, the midpoint moves left
+__device__ __forceinline__ double aniso_tail_move(const GoldenTail &t, double e, double tt)
+{
+    return e - __hiloint2double(__double2hiint(t.mid) | (__double2hiint(tt) & 0x80000000), __double2loint(t.mid));
+}
+
+// The tail of a step that has a pass inside the band: same passes, rolled, a pass inside the band decided out of line.
+template <class TIE>
+static __device__ __noinline__ double golden_aniso_tail_ties(const CostAnisoFast cost, const TIE ref, const AnisoTail a,
+                                                             double tie2, double theta, double st, double ct)
+{
+    double e = a.e0;
+    int k = RTB_GOLDEN_TAIL_K1;
+    for (;;) {
+        bool band = false;
+#pragma unroll 1
+        for (; k < RTB_GOLDEN_ITERS; ++k) {
+            double tt;
+            if (aniso_tail_in_band(a, kGoldenTail[k], e, tt)) { band = true; break; }
+            e = aniso_tail_move(kGoldenTail[k], e, tt);
+        }
+        if (!band) break;
+        const bool left = golden_trig_tie(cost, ref, tie2, theta, st, ct, k);
+        e = __dadd_rn(e, left ? -kGoldenTail[k].mid : kGoldenTail[k].mid);
+        ++k;
+    }
+    return e;
+}
+
+template <class TIE>
+__device__ __forceinline__ bool golden_aniso_tail(const CostAnisoFast &cost, const TIE &ref, double scale, double tie2,
+                                                  double theta, double st, double ct, const TrigState &g, double &th_out,
+                                                  double &s_out, double &c_out)
+{
+    constexpr int K1 = RTB_GOLDEN_TAIL_K1;
+    const double qK = kGoldenQ[K1], WK = qK * (1.0 / (RTB_GOLDEN_RHO - 0.5));
+    // Newton on the first derivative from the kept probe W: the error goes e -> (kappa / 2) e^2 per step, from at most
+    // 0.62 WK; three steps reach 1e-8 unless kappa is large AND x* sits at the far end of the bracket: then a fourth
+    double F1, F2a, F2b, F2c, f, s1, c1, s2, c2;
+    aniso_cost_d12(cost, g.Ws, g.Wc, F1, F2a, f);
+    // (products that feed a sum are formed with __dmul_rn: a contraction into the sum that differs between the
+    // instantiations of the kernel would break the bit-equality of the output modes)
+    const double d0 = __dmul_rn(-F1, rcp_fast3(F2a));
+    rotate(g.Ws, g.Wc, d0, s1, c1);
+    aniso_cost_d12(cost, s1, c1, F1, F2b, f);
+    const double d1 = __dmul_rn(-F1, rcp_fast3(F2b));
+    rotate(s1, c1, d1, s2, c2);
+    aniso_cost_d12(cost, s2, c2, F1, F2c, f);
+    double iA = rcp_fast3(F2c);
+    double dl = __dmul_rn(-F1, iA);                 // the last step
+    double delta = __dadd_rn(d0, __dadd_rn(d1, dl)); // x* - W
+    if (!(fabs(dl) <= 1e-8) && fabs(dl) <= 1e-3) {
+        rotate(g.Ws, g.Wc, delta, s1, c1);
+        aniso_cost_d12(cost, s1, c1, F1, F2c, f);
+        iA = rcp_fast3(F2c);
+        dl = __dmul_rn(-F1, iA);
+        delta = __dadd_rn(delta, dl);
+    }
+    const double kap = 2.0 * __dsub_rn(F2b, F2a) * rcp_fast3(d0 * __dadd_rn(F2a, F2b));   // third / second derivative
+    AnisoTail a;
+    a.e0 = __dsub_rn(g.nl ? -qK : qK, delta);                                      // N left: W is d, the midpoint is W - q
+    // every test fails on a NaN
+    const bool ok = F2a > 0.0 && F2b > 0.0 && F2c > 0.0 && fabs(d0) <= WK && fabs(d0) >= 1e-10 && fabs(dl) <= 1e-7 &&
+                    fabs(kap) <= 64.0 && fabs(a.e0) <= 0.5000005 * WK;
+    if (!ok) return false;
+    const double g2 = cost.g2m1 + 1.0;
+    const double lam = fma(16.0, fmax(g2, rcp_fast3(g2)), 8.0);
+    const double hw = 0.5 * WK, hq = __dadd_rn(hw, qK);
+    a.kaph = 0.5 * kap;
+    a.apx = lam * fma(fabs(d0), fma(0.5 * hw, hw, kGoldenTail[K1].q26), (hq * hq * hq) * (1.0 / 3.0)) *
+            rcp_fast3(kGoldenTail[K1].r2);
+    const double ties = RTB_TIE_EPS * scale;
+    a.na = (0.3125 * ties) * sqrt_fast(2.0 * f) * iA;                      // 1.25 TIE sqrt(2 f*) / (4 F2)
+    a.nb = fma((1.25 * 1.556) * ties, rsqrt_fast3(F2c), fma(fabs(kap) + 2.0, dl * dl, RTB_TIE_FLOOR));
+    double e = a.e0;
+    bool tie = false;
+#pragma unroll
+    for (int k = K1; k < RTB_GOLDEN_ITERS; ++k) { // straight-line: the table entries are constant-bank operands
+        double tt;
+        tie |= aniso_tail_in_band(a, kGoldenTail[k], e, tt);
+        e = aniso_tail_move(kGoldenTail[k], e, tt);
+    }
+    if (tie) e = golden_aniso_tail_ties(cost, ref, a, tie2, theta, st, ct);
+    th_out = __dadd_rn(theta, __dadd_rn(g.m, __dsub_rn(e, a.e0)));
+    rotate(g.Ws, g.Wc, __dadd_rn(delta, e), s_out, c_out);                           // the final midpoint is x* + e = W + delta + e
+    return true;
+}
+
+template <class F, class TIE>
+__device__ __forceinline__ double golden_trig(const F &cost, const TIE &ref, double scale, double theta, double st,
+                                              double ct, double &s_out, double &c_out)
+{
+    const double tie2 = (RTB_TIE_EPS * scale) * (RTB_TIE_EPS * scale);
+    TrigState g;
+    trig_init(cost, st, ct, g);
+    int k = 0;
+#ifndef RTB_NO_GOLDEN_TAIL
+    if constexpr (std::is_same<F, CostAnisoFast>::value) {
+        golden_trig_passes(cost, ref, tie2, theta, st, ct, g, k, RTB_GOLDEN_TAIL_K1);
+        double th;
+        if (golden_aniso_tail(cost, ref, scale, tie2, theta, st, ct, g, th, s_out, c_out)) return th;
+    }
+#endif
+    golden_trig_passes(cost, ref, tie2, theta, st, ct, g, k, RTB_GOLDEN_ITERS);
     // (a+b)/2 lies half a probe distance from the kept probe: to its left when the kept probe is d (N is c)
     const double e = g.nl ? -RTB_GOLDEN_FINAL_HALF : RTB_GOLDEN_FINAL_HALF, e2h = 0.5 * e * e;
     s_out = fma(-g.Ws, e2h, fma(g.Wc, e, g.Ws));

@@ -209,7 +209,7 @@ __device__ __forceinline__ bool ray_step(const TraceArgs &a, int64_t r, double g
     q.dist_sim += dist;
     q.dist_real += h;
     // RT:871-875
-    const double nray = s.coef * s.n;
+    const double nray = __dmul_rn(s.coef, s.n); // used twice: no contraction into the sum below (bit-equal output modes)
     q.T = q.T + dist * (q.nray_prev + nray) / 2.0;
     q.nray_prev = nray;
     q.last_i = i;
