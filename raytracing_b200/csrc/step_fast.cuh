@@ -297,7 +297,7 @@ struct AnisoTail {
 
 __device__ __forceinline__ bool aniso_tail_in_band(const AnisoTail &a, const GoldenTail &t, double e, double &tt)
 {
-    tt = fma(a.kaph, fma(e, e, 2.0 * t.q26), e);
+    tt = fma(a.kaph, fma(e, e, t.q23), e);
     const double bd = fma(a.apx, t.r2, fma(a.na, t.invq, a.nb));
     return (__double2hiint(tt) & 0x7fffffff) <= __double2hiint(bd);
 }
@@ -329,6 +329,24 @@ static __device__ __noinline__ double golden_aniso_tail_ties(const CostAnisoFast
         ++k;
     }
     return e;
+}
+
+// Passes K .. RTB_GOLDEN_ITERS - 1 in a straight line; `tie` collects whether any of them was inside the band.  |t| is
+// compared as a float: its high word re-biased (truncated towards zero: the band only grows); a |t| below the float
+// range counts as inside.
+template <int K>
+__device__ __forceinline__ void aniso_tail_unrolled(double kaph, float apx, float na, float nb, double &e, bool &tie)
+{
+    if constexpr (K < RTB_GOLDEN_ITERS) {
+        typedef GoldenTailC<K> C;
+        const double tt = fma(kaph, fma(e, e, C::q23), e);
+        const float bd = fmaf(apx, C::r2, fmaf(na, C::invq, nb));
+        const int hi = __double2hiint(tt);
+        tie |= (((hi & 0x7fffffff) - 0x38000000) << 3) <= __float_as_int(bd);
+        const double mid = C::mid; // RT:189: f(c) < f(d), i.e. t > 0: b = d, the midpoint moves left
+        e -= __hiloint2double(__double2hiint(mid) | (hi & 0x80000000), __double2loint(mid));
+        aniso_tail_unrolled<K + 1>(kaph, apx, na, nb, e, tie);
+    }
 }
 
 template <class TIE>
@@ -371,19 +389,16 @@ __device__ __forceinline__ bool golden_aniso_tail(const CostAnisoFast &cost, con
     const double lam = fma(16.0, fmax(g2, rcp_fast3(g2)), 8.0);
     const double hw = 0.5 * WK, hq = __dadd_rn(hw, qK);
     a.kaph = 0.5 * kap;
-    a.apx = lam * fma(fabs(d0), fma(0.5 * hw, hw, kGoldenTail[K1].q26), (hq * hq * hq) * (1.0 / 3.0)) *
+    a.apx = lam * fma(fabs(d0), fma(0.5 * hw, hw, 0.5 * kGoldenTail[K1].q23), (hq * hq * hq) * (1.0 / 3.0)) *
             rcp_fast3(kGoldenTail[K1].r2);
     const double ties = RTB_TIE_EPS * scale;
     a.na = (0.3125 * ties) * sqrt_fast(2.0 * f) * iA;                      // 1.25 TIE sqrt(2 f*) / (4 F2)
     a.nb = fma((1.25 * 1.556) * ties, rsqrt_fast3(F2c), fma(fabs(kap) + 2.0, dl * dl, RTB_TIE_FLOOR));
     double e = a.e0;
     bool tie = false;
-#pragma unroll
-    for (int k = K1; k < RTB_GOLDEN_ITERS; ++k) { // straight-line: the table entries are constant-bank operands
-        double tt;
-        tie |= aniso_tail_in_band(a, kGoldenTail[k], e, tt);
-        e = aniso_tail_move(kGoldenTail[k], e, tt);
-    }
+    // the band in single precision, rounded up (a bound): its FFMAs take their constants as immediates
+    const float up = 1.000001f;
+    aniso_tail_unrolled<K1>(a.kaph, __double2float_ru(a.apx) * up, __double2float_ru(a.na) * up, __double2float_ru(a.nb) * up, e, tie);
     if (tie) e = golden_aniso_tail_ties(cost, ref, a, tie2, theta, st, ct);
     th_out = __dadd_rn(theta, __dadd_rn(g.m, __dsub_rn(e, a.e0)));
     rotate(g.Ws, g.Wc, __dadd_rn(delta, e), s_out, c_out);                           // the final midpoint is x* + e = W + delta + e

@@ -24,6 +24,9 @@ namespace rtb {
 #ifndef RTB_MIN_BLOCKS
 #define RTB_MIN_BLOCKS 5 // default kernels: <= 96 registers -> 5 blocks of 128 threads per SM
 #endif
+// The golden-section steppers (op8-op11) carry the search state on top of the ray's: with 128 registers (4 blocks per
+// SM) their pass loop has no spill traffic, worth more than the fifth block (measured +2..5 %, op9 / op10 / op11).
+constexpr int min_blocks_of(int method) { return updater_of(method) >= 4 ? 4 : RTB_MIN_BLOCKS; }
 #ifndef RTB_QUEUE_MIN_BLOCKS
 #define RTB_QUEUE_MIN_BLOCKS 5
 #endif
@@ -317,7 +320,7 @@ __device__ __forceinline__ void ray_finish(const TraceArgs &a, int64_t r, double
 // recurrence): the parity anchor.  !EXACT = default B200 form (step_fast.cuh).
 // TMODE: 0 = no trajectory, 1 = trajectory by per-lane stores, 2 = trajectory staged in shared memory + TMA stores.
 template <int METHOD, bool ISO, int TMODE, bool EXACT, int EXTRA>
-__global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : TMODE ? RTB_TRAJ_MIN_BLOCKS : RTB_MIN_BLOCKS)
+__global__ void __launch_bounds__(RTB_BLOCK, EXACT ? (4 * 128) / RTB_BLOCK : TMODE ? RTB_TRAJ_MIN_BLOCKS : min_blocks_of(METHOD))
 trace_kernel(const __grid_constant__ TraceArgs a)
 {
     constexpr bool TRAJ = TMODE != 0;
