@@ -8,6 +8,10 @@ rows = list(csv.reader(open(sys.argv[1])))
 steps = int(sys.argv[2]) / 32
 name = rows[0][1] if len(rows[0]) > 1 else ""
 hdr, data = rows[1], rows[2:]
+for n_, r_ in enumerate(data):   # a capture of several launches: keep the first listing
+    if len(r_) < len(hdr) or r_ == hdr:
+        data = data[:n_]
+        break
 isrc, iex, ismp = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
 print("# ncu source page (SASS) of %s" % name)
 print("# condensed by tools/ncu_source_summary.py from the capture of tools/gpu_ncu_final.sh (ncu --set full --import-source on);")
