@@ -242,7 +242,8 @@ struct Staging {
     void copy_back()
     {
         for (auto &b : back) {
-            if (b.rows == 1 && b.bytes >= ((size_t)256 << 20)) { // large and contiguous: pageable destination?
+            if (b.rows == 1 && b.bytes >= ((size_t)16 << 20)) { // large and contiguous: pageable destination?  (61 MB of
+                // configs[0]'s s_ray: 15 ms by cudaMemcpy into fresh pages, 3 ms through the bounce buffers)
                 cudaPointerAttributes at;
                 const bool pageable = cudaPointerGetAttributes(&at, b.host) != cudaSuccess || at.type == cudaMemoryTypeUnregistered;
                 (void)cudaGetLastError();
