@@ -72,6 +72,10 @@ typedef struct {
                                  compact when lanes finish (warp ballot + refill of the dead lanes).  Opt-in: meant for
                                  fans whose neighbouring rays differ widely in length, but on every fan measured on B200
                                  the static grid is as fast or faster; results are bit-identical either way */
+#define RTB_F_SORT_FAN 32u    /* rtb_trace, FINAL-type outputs (s_ray NULL): the library orders the rays by (x0, y0, theta0)
+                                 before the launch and hands every result back at the caller's ray index -- the remedy for
+                                 unsorted fans (neighbouring rays share a warp: shuffled 2^20-ray fan 73.5 -> 15.9 ms).  The
+                                 reference has no counterpart (it traces ray by ray, RT:807); results are bit-identical */
 
 typedef struct {
     int32_t method;     /* 1..11 = op1..op11 (RT:469-764); the shim maps function objects to ids  */

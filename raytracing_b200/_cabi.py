@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTB_LIB_PATH") or os.path.join(_HERE, "csrc", "librtb.so")  # override: kernel tuning only
 
 RTB_PTR_HOST, RTB_PTR_DEVICE = 0, 1
-RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO, RTB_F_STATIC_GRID, RTB_F_RAY_QUEUE = 1, 2, 4, 8, 16
+RTB_F_INTERFACE, RTB_F_EXACT_BASIS, RTB_F_NO_TAIL_ZERO, RTB_F_STATIC_GRID, RTB_F_RAY_QUEUE, RTB_F_SORT_FAN = 1, 2, 4, 8, 16, 32
 RTB_OPT_QUEUE, RTB_OPT_TRAJ_STORE, RTB_OPT_SHOOT_GROUPS, RTB_OPT_SHOOT_SPECULATE = 1, 2, 3, 4
 RTB_SWEEP_SNELL, RTB_SWEEP_CLOSURE, RTB_SWEEP_PX_CV = 1, 2, 3
 RTB_ABI_VERSION = 2

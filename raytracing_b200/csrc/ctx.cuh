@@ -98,6 +98,10 @@ int rtb_launch(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, TraceArgs a, 
 int rtb_trace_core(rtb_ctx *ctx, cudaStream_t st, const rtb_params *p, const TraceArgs &a, double *d_err,
                    bool has_errors, bool want_err, bool traj, int stride, Staging &sg, int64_t &launches);
 
+// rtb_trace with RTB_F_SORT_FAN (sortfan.cu): order the fan, trace, scatter the results back.
+int rtb_trace_sorted(rtb_ctx *ctx, const rtb_params *p, const double *theta0, const double *x0, const double *y0, int64_t R,
+                     double *d_ray, double *errors, double *last_row, double *px_stats, rtb_stats *stats);
+
 // Field construction pieces defined in rtb.cu and shared with fit.cu.
 void rtb_free_field(rtb_ctx *ctx);
 int rtb_make_axis(rtb_ctx *ctx, const double *t, int n, int k, DevAxis *ax);

@@ -439,8 +439,10 @@ extern "C" int rtb_trace(rtb_ctx *ctx, const rtb_params *p, const double *theta0
     if (s_ray && (p->out_stride < 1)) return fail(ctx, RTB_ERR_ARG, "rtb_trace: out_stride must be >= 1");
     if (s_ray && (p->steps || p->max_sizes)) return fail(ctx, RTB_ERR_ARG, "rtb_trace: s_ray with per-ray steps");
     if (!(p->step > 0) && !p->steps) return fail(ctx, RTB_ERR_ARG, "rtb_trace: step must be > 0");
+    if ((p->flags & RTB_F_SORT_FAN) && s_ray) return fail(ctx, RTB_ERR_ARG, "rtb_trace: RTB_F_SORT_FAN with s_ray (FINAL-type outputs only)");
     if (stats) std::memset(stats, 0, sizeof(*stats));
     if (R == 0) return RTB_OK;
+    if ((p->flags & RTB_F_SORT_FAN) && R > 1) return rtb_trace_sorted(ctx, p, theta0, x0, y0, R, d_ray, errors, last_row, px_stats, stats);
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     const bool host = p->ptr_kind == RTB_PTR_HOST;

@@ -304,16 +304,12 @@ class Engine:
         (device pointers; outputs are then torch tensors too).  `out` may supply preallocated
         outputs by name.  Returns TraceResult.
 
-        sort_fan (torch tensors, no trajectory): trace the rays in order of (x0, y0, theta0) and hand the results back
-        in the caller's order.  Rays are independent, so the results are the same bits; what changes is that
-        neighbouring lanes then walk through the same field cells -- an unsorted fan is 5x slower than a sorted one
-        because every warp fetches 32 different cell records per step.  The permutation is a
-        torch.sort on the device; it costs about as much as 10 ray-steps per ray.
+        sort_fan (no trajectory; RTB_F_SORT_FAN): the library traces the rays in order of (x0, y0, theta0) and hands the
+        results back in the caller's order.  Rays are independent, so the results are the same bits; what changes is
+        that neighbouring lanes then walk through the same field cells -- an unsorted fan is 5x slower than a sorted one
+        because every warp fetches 32 different cell records per step.  The ordering is three
+        radix sorts on the device; it costs about as much as 10 ray-steps per ray.
         """
-        if sort_fan and _is_torch(theta0) and not full and steps is None:
-            return self._trace_sorted(method, theta0, x0, y0, step, max_size, gamma, box, interface=interface,
-                                      want_last_row=want_last_row, want_px_stats=want_px_stats, want_errors=want_errors,
-                                      exact=exact, static_grid=static_grid, ray_queue=ray_queue)
         m = method_id(method)
         dev = _is_torch(theta0)
         out = dict(out or {})
@@ -346,7 +342,8 @@ class Engine:
         last_row = out.get("last_row", empty(6, R) if want_last_row else None)
         px_stats = out.get("px_stats", empty(3, R) if want_px_stats else None)
         flags = (_cabi.RTB_F_INTERFACE if interface else 0) | (_cabi.RTB_F_EXACT_BASIS if exact else 0) | \
-                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO) | (_cabi.RTB_F_STATIC_GRID if static_grid else 0) | (_cabi.RTB_F_RAY_QUEUE if ray_queue else 0)
+                (0 if tail_zero else _cabi.RTB_F_NO_TAIL_ZERO) | (_cabi.RTB_F_STATIC_GRID if static_grid else 0) | (_cabi.RTB_F_RAY_QUEUE if ray_queue else 0) | \
+                (_cabi.RTB_F_SORT_FAN if sort_fan else 0)
         steps_a = max_sizes_a = None
         if steps is not None:
             if dev:
@@ -367,24 +364,6 @@ class Engine:
                                         ptr(d_ray), ptr(errors), ptr(last_row), ptr(px_stats), C.byref(stats)))
         return TraceResult(s_ray=s_ray, d_ray=d_ray, errors=errors, last_row=last_row, px_stats=px_stats,
                            stats=self._stats(stats))
-
-    def _trace_sorted(self, method, theta0, x0, y0, step, max_size, gamma, box, **kw):
-        import torch
-        R = theta0.numel()
-        bc = lambda a: a if _is_torch(a) else torch.full((R,), float(a), dtype=torch.float64, device=theta0.device)
-        x0, y0 = bc(x0), bc(y0)
-        perm = torch.argsort(theta0, stable=True)             # least significant key first
-        for key in (y0, x0):
-            if not bool((key == key[0]).all()):
-                perm = perm[torch.argsort(key[perm], stable=True)]
-        r = self.trace(method, theta0[perm].contiguous(), x0[perm].contiguous(), y0[perm].contiguous(), step, max_size,
-                       gamma, box, full=False, **kw)
-        inv = torch.empty_like(perm)
-        inv[perm] = torch.arange(R, device=perm.device)
-        for name in ("d_ray", "last_row", "px_stats", "errors"):
-            if r[name] is not None:
-                r[name] = r[name][..., inv].contiguous()
-        return r
 
     # -- batched two-point shooting search (include/rtb.h rtb_shoot_*; parity-unpinned) --
     def _shoot_args(self, method, src, steps, max_sizes, targets, gamma, box, exact, like):

@@ -168,18 +168,43 @@ def test_ray_queue_equals_static_grid(engine, case):
 
 
 def test_sort_fan_gives_the_same_results(engine):
-    """Engine.trace(sort_fan=True): an unsorted fan traced in sorted order, results handed back in the caller's order."""
+    """RTB_F_SORT_FAN (Engine.trace(sort_fan=True)): an unsorted fan traced in the order of (x0, y0, theta0) inside the
+    library, results handed back at the caller's ray index: the same bits as the unsorted call -- device and host
+    pointers, shuffled angles, scattered start points, per-ray DELTA_S candidates, the Snell metric."""
     import torch
     s = scenario_setup("3")
     engine.set_field(s["z"], s["grd"])
     R = (1 << 16) + 5
+    rng = np.random.default_rng(11)
     th, x0, y0 = rt.make_fan("3", R)
-    th = np.random.default_rng(11).permutation(th)
+    th = rng.permutation(th)
     kw = dict(full=False, want_px_stats=True)
     a = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], **kw)
     b = engine.trace(6, *_dev(th, x0, y0), s["step"], s["M"], s["gamma"], s["box"], sort_fan=True, **kw)
     for name in ("d_ray", "last_row", "px_stats"):
         assert torch.equal(torch.nan_to_num(a[name], nan=-1.0), torch.nan_to_num(b[name], nan=-1.0)), name
+    assert a.stats["ray_steps"] == b.stats["ray_steps"]
+    # host pointers; start points on three lines, negative and repeated angles, two DELTA_S candidates mixed per ray
+    R = 5000
+    th = rng.uniform(-0.3, 1.5, R); th[::7] = th[3]
+    x0 = rng.choice([-2.0, -1.5, -1.0], R); y0 = rng.choice([-2.0, -1.75], R)
+    steps = rng.choice([s["step"], 2.5 * s["step"]], R)
+    msz = np.where(steps == s["step"], s["M"], s["M"] // 2).astype(np.int64)
+    kw = dict(full=False, want_px_stats=True, steps=steps, max_sizes=msz)
+    a = engine.trace(6, th, x0, y0, None, s["M"], s["gamma"], s["box"], **kw)
+    b = engine.trace(6, th, x0, y0, None, s["M"], s["gamma"], s["box"], sort_fan=True, **kw)
+    for name in ("d_ray", "last_row", "px_stats"):
+        assert np.array_equal(a[name], b[name], equal_nan=True), name
+    s1 = scenario_setup("1")
+    engine.set_field(s1["z"], s1["grd"])
+    th, x0, y0 = rt.make_fan("1", 3000)
+    pm = rng.permutation(3000)
+    a = engine.trace(6, th[pm], x0[pm], y0[pm], s1["step"], s1["M"], s1["gamma"], s1["box"], interface=True, full=False)
+    b = engine.trace(6, th[pm], x0[pm], y0[pm], s1["step"], s1["M"], s1["gamma"], s1["box"], interface=True, full=False,
+                     sort_fan=True)
+    assert np.array_equal(a.errors, b.errors, equal_nan=True) and np.array_equal(a.d_ray, b.d_ray)
+    with pytest.raises(Exception, match="RTB_F_SORT_FAN"):
+        engine.trace(6, th, x0, y0, s1["step"], 50, s1["gamma"], s1["box"], full=True, sort_fan=True)
 
 
 # ------------------------------------------------------------------------------------------------------------------

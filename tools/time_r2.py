@@ -46,7 +46,7 @@ for uc, lg, m, kw, tag in (("2", 20, 6, {}, "fisheye 2^20 op6 final"), ("2", 20,
         print("%-32s %s %9.3f ms  %.4e ray-steps/s" % (tag, name, ms, steps / ms * 1e3), flush=True)
 eng.set_option("queue", 0)
 
-# the remedy for an unsorted fan: trace it in sorted order (Engine.trace(sort_fan=True): torch.sort + gather + scatter)
+# the remedy for an unsorted fan: trace it in sorted order (Engine.trace(sort_fan=True) = RTB_F_SORT_FAN: radix sorts + gather + scatter inside rtb_trace)
 uc = "3"
 eng.set_field(*rt.build_field(uc))
 c = rt.scenario_constants(uc)
