@@ -113,6 +113,32 @@ def test_dense_fan_vs_oracle_and_reference(engine, golden_traj, sensitivity, uc,
             assert torch.equal(st.d_ray, r.d_ray) and torch.equal(st.last_row, r.last_row)
 
 
+@pytest.mark.parametrize("gamma", [0.6, 1.7, 3.0, 4.5])
+@pytest.mark.parametrize("m", [10, 11])
+def test_anisotropic_golden_other_gammas(engine, sensitivity, m, gamma):
+    """The anisotropic golden search (evaluating passes + the Taylor tail, step_fast.cuh golden_aniso_tail) on the aniso
+    scenario's field with other anisotropy factors than the scenario's 3: the bound on the expansion's error depends on
+    gamma.  A dense run of 4096 rays (staged warps) against the oracle on sampled rays; step counts exact."""
+    s = scenario_setup("4")
+    engine.set_field(s["z"], s["grd"])
+    tol = tolerances(sensitivity, "4", m)
+    n = 4096
+    th, x0, y0 = rt.make_fan("4", 1 << 20, 300000, 300000 + n)
+    s = dict(s, gamma=gamma)
+    r = engine.trace(m, *_dev(th, x0, y0), s["step"], s["M"], gamma, s["box"], full=False, want_px_stats=True)
+    d, last = r.d_ray.cpu().numpy(), r.last_row.cpu().numpy()
+    assert r.stats["nonfinite_rays"] == 0
+    pick = np.unique(np.concatenate([np.arange(1000, 1040), np.linspace(0, n - 1, 24).astype(int)]))
+    o = _oracle_final(s, "4", m, th[pick], x0[pick], y0[pick])
+    tol_m, unstable = _measured_tolerance(s, "4", m, th[pick], x0[pick], y0[pick], o, tol)
+    assert unstable.mean() < 0.1
+    ok = ~unstable
+    what = "aniso gamma %.1f op%d" % (gamma, m)
+    assert np.array_equal(d[2, pick][ok], o["d_ray"][2][ok]), what + " steps"
+    assert_close(last[:, pick][:, ok], o["final"][:, ok], tol_m["all"], what + " last_row")
+    assert_close(d[:2, pick][:, ok], o["d_ray"][:2, ok], tol_m["d_ray"], what + " d_ray")
+
+
 def test_interface_dense_fan_vs_oracle(engine, sensitivity):
     """interface 2^18 rays op6 + Snell metric in FINAL mode (two-pass with checkpoints) on the queue kernels."""
     from oracle import rt_oracle as O
