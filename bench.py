@@ -668,6 +668,20 @@ def run_interface_default(ctx):
             "gpu_launches": int(r.stats["launches"]) * n}
 
 
+def shoot_roofline(ctx, method, per_gpu, kernel_ms, clocks, K):
+    """The FP64 roofline block of the trace kernel (executed counts from the dense interface capture) plus what ncu
+    measured on a launch of the refinement itself: its probe rays sit in different field cells, so the launch is bound
+    by the L1 data pipe / L1 misses, not by FP64."""
+    rb = roofline_block(method, "trace_kernel<%d,iso,final,exit>" % method, per_gpu, kernel_ms, ctx["fp64_peak"],
+                        (clocks or {}).get("sm_mhz"), ctx["ncu"], ctx["ncu_note"], "op6_exit_interface", K.F_ALG)
+    k = (ctx["ncu"] or {}).get("kernels", {}).get("shoot_refine")
+    if k:
+        rb["refine_launch"] = {"bound_measured": "l1 data pipe", "ncu_l1_data_pipe_frac": k.get("lsu_pipe_frac"),
+                               "ncu_fp64_pipe_active_frac": k.get("fp64_pipe_active_frac"), "ncu_l1_hit_rate": k.get("l1_hit_rate"),
+                               "ncu_issue_active_frac": k.get("issue_active_frac"), "source": k.get("source")}
+    return rb
+
+
 def run_shoot_config(ctx, n_cand=200, A=4096, Tn=4096, method=6):
     import torch
     D, eng, rt, K, args = ctx["D"], ctx["eng"], ctx["rt"], ctx["K"], ctx["args"]
@@ -715,9 +729,7 @@ def run_shoot_config(ctx, n_cand=200, A=4096, Tn=4096, method=6):
                             "all_gather, x%d" % world) if world > 1 else "1 GPU",
             "check": {"max_abs_theta_minus_truth_finest": float(np.abs(th[0] - true)[ok].max()),
                       "max_miss_finest": float(miss[0][ok].max())},
-            "roofline": roofline_block(method, "trace_kernel<%d,iso,final,exit>" % method, per_gpu, k_max / steps,
-                                       ctx["fp64_peak"], (clocks or {}).get("sm_mhz"), ctx["ncu"], ctx["ncu_note"],
-                                       "op6_exit_interface", K.F_ALG),
+            "roofline": shoot_roofline(ctx, method, per_gpu, k_max / steps, clocks, K),
             "e2e": {"value": total_steps / (t_max * 1e-3), "unit": UNIT, "ms_per_step": t_max / steps,
                     "h2d_bytes_per_step": bytes_io[0], "d2h_bytes_per_step": bytes_io[1] if world == 1 else 0,
                     "api": "raytracing_b200.shooting_search: numpy arrays in (angles, targets, candidates), %s"

@@ -13,7 +13,8 @@ done
 python tools/ncu_summary.py table $O/bracket_shoot.raw.csv profiles/r2_ncu_bracket_kernel.csv
 python tools/ncu_summary.py table $O/shoot_refine.raw.csv profiles/r2_ncu_shoot_refine.csv
 python tools/ncu_source_summary.py $O/op11_stats_aniso.source.csv $(grep -o "ray_steps=[0-9]*" $O/op11_stats_aniso.plain.log | cut -d= -f2) > profiles/r2_ncu_source_op11_stats_aniso.txt
-python tools/ncu_summary.py json profiles/ncu_latest.json $(for k in $P; do echo -n "$k=/tmp/ncuj/r2_ncu_$k "; done)
+cp $O/shoot_refine.raw.csv /tmp/ncuj/r2_ncu_shoot_refine.raw.csv; cp $O/shoot_refine.plain.log /tmp/ncuj/r2_ncu_shoot_refine.plain.log
+python tools/ncu_summary.py json profiles/ncu_latest.json $(for k in $P shoot_refine; do echo -n "$k=/tmp/ncuj/r2_ncu_$k "; done)
 python tools/ncu_source_summary.py $O/op6_final_fisheye.source.csv 953155584 > profiles/r2_ncu_source_op6_final_fisheye.txt
 python tools/sass_loop.py raytracing_b200/csrc/trace_m6.o trace_kernelILi6ELb1ELi0ELb0ELi0E > profiles/r2_sass_loop_op6_final.txt
 cuobjdump -sass raytracing_b200/csrc/trace_m6.o 2>/dev/null | awk '/Function : .*trace_kernelILi6ELb1ELi0ELb0ELi0E/{f=1} f&&/Function : /&&!/trace_kernelILi6ELb1ELi0ELb0ELi0E/{f=0} f' | grep -E "^\s+/\*[0-9a-f]{4}\*/" | sed 's/ *\/\* 0x[0-9a-f]* \*\///' >> profiles/r2_sass_loop_op6_final.txt

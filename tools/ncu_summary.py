@@ -49,19 +49,20 @@ def kernel_entry(prefix, key):
         x = float(v.replace(",", ""))
         return x * UNIT_SCALE.get(u, 1.0) if scale else x
     m = re.search(r"ray_steps=(\d+)", open(prefix + ".plain.log").read())
-    steps = int(m.group(1))
+    steps = int(m.group(1)) if m else None     # None: one launch out of many (shooting refinement): no per-step figures
     cyc = num("smsp__cycles_elapsed.avg")
-    per = lambda op: num("smsp__sass_thread_inst_executed_op_%s_pred_on.sum.per_cycle_elapsed" % op) * cyc / steps
+    per = lambda op: num("smsp__sass_thread_inst_executed_op_%s_pred_on.sum.per_cycle_elapsed" % op) * cyc / steps if steps else None
     return {
         "kernel": col["Kernel Name"][1], "workload": key, "ray_steps": steps,
         "ncu_duration_ms": num("gpu__time_duration.sum", True),
         "dfma": per("dfma"), "dmul": per("dmul"), "dadd": per("dadd"),
-        "inst_per_warp_step": num("smsp__inst_executed.sum") / (steps / 32.0),
+        "inst_per_warp_step": num("smsp__inst_executed.sum") / (steps / 32.0) if steps else None,
         "fp64_pipe_active_frac": num("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active") / 100.0,
         "issue_active_frac": num("smsp__issue_active.avg.pct_of_peak_sustained_active") / 100.0,
         "lsu_pipe_frac": num("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed") / 100.0,
         "warps_active_frac": num("sm__warps_active.avg.pct_of_peak_sustained_active") / 100.0,
         "registers": int(num("launch__registers_per_thread")),
+        "l1_hit_rate": num("l1tex__t_sector_hit_rate.pct") / 100.0,
         "dram_bytes_per_launch": num("dram__bytes_read.sum", True) + num("dram__bytes_write.sum", True),
         "source": "profiles/" + os.path.basename(prefix) + ".csv",
     }
