@@ -90,7 +90,7 @@ print("kappa err", np.abs(kap - kap_ex)[ok].max(), "bound used", (lam_b * np.abs
 e_ = (x0 - q[K1]) - xs                      # midpoint of the probes (x0 is d) minus the minimiser
 kap_err = lam_b * np.abs(dl0)               # secant midpoint is dl0/2 from x0, x* is dl0 away: <= lam |dl0|
 noise_a = 1.25 * TIE_EPS * scale * np.sqrt(2 * fst) / (4 * F2c)          # / q
-noise_b = 1.25 * TIE_EPS * scale * 2.0 * np.sqrt(2 * F2c) / (4 * F2c) + 2e-14 + (np.abs(kap) + 2) * dl2 * dl2
+noise_b = 1.25 * TIE_EPS * scale * 4.4 * np.sqrt(2 * F2c) / (4 * F2c) + 2e-14 + (np.abs(kap) + 2) * dl2 * dl2
 tie_apx = np.zeros(N, bool); tie_noise = np.zeros(N, bool); first_apx = np.zeros(ITERS)
 mism = np.zeros(N, bool); tie_new = np.zeros(N, bool); tie_old = np.zeros(N, bool); old_in_new = 0
 for k in range(K1, ITERS):
