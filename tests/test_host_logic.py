@@ -146,3 +146,18 @@ def test_cli_menu_mapping_and_results_wording(capsys):
     s = np.zeros((4, 6, 3)); s[-1, 0, 0] = 1.0
     assert cli.results_metric("2", s, None) == 0.0
     assert cli.results_metric("1", None, np.array([0.1, 0.3])) == pytest.approx(0.2)
+
+
+@pytest.mark.parametrize("gamma", [0.6, 3.0])
+def test_golden_tail_decision_rule(gamma):
+    """The rule the anisotropic golden search uses for its passes >= 12 (step_fast.cuh golden_aniso_tail): the sign of
+    t = e + kappa (e^2/2 + q^2/6) outside a band.  numpy restatement (tools/proto/golden_tail.py) against the evaluating
+    search on random steps: no decision outside the band differs, and every pass the evaluating search would hand to the
+    reference-order comparison lies inside the band."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tools", "proto"))
+    import golden_tail
+    differ, missed, tie_new, tie_old = golden_tail.run(K1=12, gamma=gamma, N=20000, verbose=False)
+    assert differ == 0 and missed == 0
+    assert tie_new <= tie_old + 0.05          # the wider band costs few extra out-of-line decisions
